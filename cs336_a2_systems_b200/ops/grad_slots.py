@@ -1,0 +1,71 @@
+"""Gradient destination registry ("arena-backed gradients").
+
+The reference flattens a bucket's gradients with ``torch.cat`` before each all-reduce and
+re-materialises ``param.grad`` from the reduced buffer afterwards
+(``ddp_bucketed_overlapped_sharded.py:297,311-314``).  Here whoever owns a flat gradient
+buffer (a DDP bucket in NVLink symmetric memory, a flat optimizer arena) registers, per
+parameter, the view its gradient should be *produced into*.  The weight-gradient kernels
+(tcgen05 wgrad GEMM epilogue, RMSNorm/embedding backward) look the slot up and write there
+directly, and autograd's AccumulateGrad adopts the returned view as ``param.grad`` without a
+copy — flatten/unflatten vanish.
+
+A slot can be used once per backward (``claim``); a second producer for the same parameter
+(tied weights, gradient accumulation) gets ``None`` and falls back to an ordinary temporary
+that autograd accumulates, so semantics never change.
+"""
+
+from __future__ import annotations
+
+import torch
+from torch.utils.weak import WeakIdKeyDictionary
+
+# identity-keyed (tensor == is elementwise, so an ordinary WeakKeyDictionary cannot hold tensors)
+_slots = WeakIdKeyDictionary()
+
+
+class _Slot:
+    __slots__ = ("base", "offset", "shape", "claimed")
+
+    def __init__(self, base: torch.Tensor, offset: int, shape):
+        self.base, self.offset, self.shape, self.claimed = base, offset, tuple(shape), False
+
+    def view(self) -> torch.Tensor:
+        n = 1
+        for s in self.shape:
+            n *= s
+        return self.base.narrow(0, self.offset, n).view(self.shape)
+
+
+def register(param: torch.Tensor, base: torch.Tensor, offset: int) -> None:
+    """``param``'s gradient lives at ``base[offset : offset+numel]`` (a 1-D flat buffer)."""
+    _slots[param] = _Slot(base, offset, param.shape)
+
+
+def unregister(param: torch.Tensor) -> None:
+    _slots.pop(param, None)
+
+
+def claim(param: torch.Tensor) -> torch.Tensor | None:
+    """Fresh view of the parameter's slot for a producer to write into, or None."""
+    s = _slots.get(param)
+    if s is None or s.claimed or param.grad is not None:
+        return None
+    s.claimed = True
+    return s.view()
+
+
+def slot_view(param: torch.Tensor) -> torch.Tensor | None:
+    s = _slots.get(param)
+    return None if s is None else s.view()
+
+
+def release_all(params=None) -> None:
+    """Start of a new step: every slot may be produced into again."""
+    if params is None:
+        for s in _slots.values():
+            s.claimed = False
+    else:
+        for p in params:
+            s = _slots.get(p)
+            if s is not None:
+                s.claimed = False

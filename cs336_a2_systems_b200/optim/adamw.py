@@ -1,0 +1,130 @@
+"""AdamW with the course library's arithmetic and state layout, plus a fused sm_100a path.
+
+Semantics (``cs336_basics/optimizer.py:30-86``): per-parameter state ``{"m", "v", "t"}`` with
+``t`` starting at 1; ``α_t = lr·√(1-β₂ᵗ)/(1-β₁ᵗ)``; ``p -= α_t·m/(√v+eps)`` and then
+``p -= lr·wd·p`` (decay AFTER the update — not ``torch.optim.AdamW``'s arithmetic).
+
+CUDA fp32 parameters take ONE multi-tensor kernel launch for the whole model
+(``csrc/adamw.cu``) instead of ~12 ATen launches per tensor: it reads a device-resident
+descriptor table, keeps the step counter and the hyper-parameters in device memory (so the
+step can live inside a CUDA graph and the LR schedule is a 4-byte async copy) and, in the
+same pass, refreshes the bf16 weight shadows the tcgen05 GEMMs read — the autocast
+weight-cast kernels disappear from the step.
+"""
+
+from __future__ import annotations
+
+import math
+from collections.abc import Callable, Iterable
+
+import torch
+
+from .. import _native
+
+
+def get_cosine_lr(it: int, max_learning_rate: float, min_learning_rate: float, warmup_iters: int,
+                  cosine_cycle_iters: int) -> float:
+    """Linear warm-up then cosine decay to ``min_learning_rate`` (optimizer.py:9-27)."""
+    if it < warmup_iters:
+        return max_learning_rate * it / warmup_iters
+    if it > cosine_cycle_iters:
+        return min_learning_rate
+    ratio = (it - warmup_iters) / (cosine_cycle_iters - warmup_iters)
+    coeff = 0.5 * (1.0 + math.cos(math.pi * ratio))
+    return min_learning_rate + coeff * (max_learning_rate - min_learning_rate)
+
+
+class AdamW(torch.optim.Optimizer):
+    def __init__(self, params: Iterable, lr: float = 1e-3, betas: tuple[float, float] = (0.9, 0.999),
+                 eps: float = 1e-8, weight_decay: float = 0.01, fused: bool | None = None):
+        if lr < 0.0:
+            raise ValueError(f"Invalid learning rate: {lr}")
+        if eps < 0.0:
+            raise ValueError(f"Invalid epsilon value: {eps}")
+        if not 0.0 <= betas[0] < 1.0:
+            raise ValueError(f"Invalid beta parameter at index 0: {betas[0]}")
+        if not 0.0 <= betas[1] < 1.0:
+            raise ValueError(f"Invalid beta parameter at index 1: {betas[1]}")
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
+        self._fused = fused
+        self._plans: dict[int, object] = {}
+
+    # ------------------------------------------------------------------ reference arithmetic
+    @staticmethod
+    def _step_param_torch(p, state, lr, b1, b2, eps, wd):
+        g = p.grad.data
+        if g.is_sparse:
+            raise RuntimeError("AdamW does not support sparse gradients")
+        t = state.get("t", 1)
+        m = state.get("m")
+        v = state.get("v")
+        if m is None:
+            m = torch.zeros_like(g)
+            v = torch.zeros_like(g)
+        m = b1 * m + (1 - b1) * g
+        v = b2 * v + (1 - b2) * torch.square(g)
+        alpha_t = lr * (math.sqrt(1 - b2 ** t) / (1 - b1 ** t))
+        p.data -= alpha_t * m / (torch.sqrt(v) + eps)
+        p.data -= lr * wd * p.data
+        state["m"], state["v"], state["t"] = m, v, t + 1
+
+    def _fusable(self, p) -> bool:
+        if self._fused is False or _native.force_torch():
+            return False
+        return p.is_cuda and p.dtype == torch.float32 and p.grad is not None and \
+            p.grad.dtype == torch.float32 and not p.grad.is_sparse and p.is_contiguous() and \
+            p.grad.is_contiguous()
+
+    @torch.no_grad()
+    def step(self, closure: Callable | None = None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        for gi, group in enumerate(self.param_groups):
+            lr, (b1, b2), eps, wd = group["lr"], group["betas"], group["eps"], group["weight_decay"]
+            fused_ps = []
+            for p in group["params"]:
+                if p.grad is None:
+                    continue
+                if self._fusable(p):
+                    fused_ps.append(p)
+                else:
+                    self._step_param_torch(p, self.state[p], lr, b1, b2, eps, wd)
+            if fused_ps:
+                self._step_fused(gi, fused_ps, lr, b1, b2, eps, wd)
+        return loss
+
+    # ------------------------------------------------------------------ fused sm_100a path
+    def _step_fused(self, gi: int, ps, lr, b1, b2, eps, wd):
+        from ..ops import native
+
+        for p in ps:
+            st = self.state[p]
+            if "m" not in st:
+                st["m"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                st["v"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                st["t"] = 1
+        plan = self._plans.get(gi)
+        key = tuple((p.data_ptr(), p.grad.data_ptr()) for p in ps)
+        if plan is None or plan.key != key:
+            t0 = self.state[ps[0]]["t"]
+            if any(self.state[p]["t"] != t0 for p in ps):
+                # mixed step counts (param added later): one plan per distinct t
+                for p in ps:
+                    self._step_param_torch(p, self.state[p], lr, b1, b2, eps, wd)
+                return
+            plan = native.AdamWPlan(ps, [p.grad for p in ps], [self.state[p]["m"] for p in ps],
+                                    [self.state[p]["v"] for p in ps], key=key, step0=t0)
+            self._plans[gi] = plan
+        plan.set_hyper(lr, b1, b2, eps, wd)
+        plan.launch()
+        for p in ps:  # host mirror of the device step counter (exact outside CUDA-graph replay)
+            self.state[p]["t"] += 1
+
+    def sync_step_from_device(self) -> None:
+        """After CUDA-graph replays the host ``t`` mirrors are stale; refresh them from the device."""
+        for gi, plan in self._plans.items():
+            t = plan.device_step()
+            for p in plan.params:
+                self.state[p]["t"] = t

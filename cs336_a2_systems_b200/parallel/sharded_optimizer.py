@@ -1,0 +1,181 @@
+"""Optimizer-state sharding (ZeRO-1-like) around an arbitrary optimizer class.
+
+Counterpart of the reference's ``ShardedStateOptimizer``
+(``ddp_bucketed_overlapped_sharded.py:322-362``): every parameter is owned by exactly one rank
+(greedy least-loaded-by-bytes assignment), only the owner keeps optimizer state and takes the
+update, and the updated values are then distributed to all ranks.
+
+What changed, B200-first:
+
+* distribution is ONE packed broadcast per owner rank and dtype (``world_size`` collectives per
+  step) instead of one blocking broadcast per parameter (435 for the XL model);
+  packing copies bits, so results stay bit-identical to the unsharded optimizer;
+* when the wrapped class is this package's ``AdamW`` and the parameters live in an NVLink
+  symmetric arena (``ShardedOptimizer.enable_symmetric(...)``), the owner's AdamW update and the
+  distribution are one kernel: it updates m, v, p for the owned shard and stores the new
+  parameter values straight into every peer's parameter memory over NVLink
+  (``csrc/comm_adamw.cu``) — the broadcast disappears;
+* a rank that owns nothing is legal, ``add_param_group`` after construction works, and
+  ``consolidated_state_dict()`` gathers the sharded state for checkpointing (the reference has none).
+"""
+
+from __future__ import annotations
+
+from collections import OrderedDict
+from typing import Any, Type
+
+import torch
+import torch.distributed as dist
+
+from .process_group import world
+
+
+class ShardedOptimizer(torch.optim.Optimizer):
+    def __init__(self, params, optimizer_cls: Type[torch.optim.Optimizer], process_group=None, **kwargs: Any):
+        self.optimizer_cls = optimizer_cls
+        self.optimizer_kwargs = kwargs
+        self.process_group = process_group
+        self.rank, self.world_size = world()
+        self._owner: dict[int, int] = {}
+        self._load = [0] * self.world_size
+        self.optimizer: torch.optim.Optimizer | None = None
+        self._symm = None
+        super().__init__(params, defaults={})
+
+    # ------------------------------------------------------------------ partitioning
+    def add_param_group(self, param_group: dict) -> None:
+        super().add_param_group(param_group)
+        group = self.param_groups[-1]
+        local = []
+        for p in group["params"]:
+            if id(p) in self._owner:
+                continue
+            owner = min(range(self.world_size), key=lambda r: (self._load[r], r))
+            self._owner[id(p)] = owner
+            self._load[owner] += p.numel() * p.element_size()
+            if owner == self.rank:
+                local.append(p)
+        if not local:
+            return
+        local_group = {k: v for k, v in group.items() if k != "params"}
+        local_group["params"] = local
+        if self.optimizer is None:
+            self.optimizer = self.optimizer_cls([local_group], **self.optimizer_kwargs)
+        else:
+            self.optimizer.add_param_group(local_group)
+
+    def owner_of(self, p: torch.Tensor) -> int:
+        return self._owner[id(p)]
+
+    # ------------------------------------------------------------------ step
+    def step(self, closure=None, **kwargs):
+        loss = None
+        if self._symm is not None:
+            loss = closure() if closure is not None else None
+            self._symm.step(self)
+            return loss
+        if self.optimizer is not None:
+            self._sync_hyperparameters()
+            loss = self.optimizer.step(closure, **kwargs) if closure is not None else self.optimizer.step(**kwargs)
+        elif closure is not None:
+            loss = closure()
+        self._distribute()
+        return loss
+
+    def _sync_hyperparameters(self) -> None:
+        """LR schedules mutate ``self.param_groups``; mirror scalar hyper-parameters into the inner groups."""
+        inner_by_first: dict[int, dict] = {}
+        for g in self.optimizer.param_groups:
+            for p in g["params"]:
+                inner_by_first[id(p)] = g
+        for g in self.param_groups:
+            for p in g["params"]:
+                ig = inner_by_first.get(id(p))
+                if ig is not None:
+                    for k, v in g.items():
+                        if k != "params":
+                            ig[k] = v
+
+    @torch.no_grad()
+    def _distribute(self) -> None:
+        if self.world_size == 1:
+            return
+        # pack per (owner, dtype, device): one broadcast each
+        packs: "OrderedDict[tuple, list[torch.Tensor]]" = OrderedDict()
+        seen = set()
+        for g in self.param_groups:
+            for p in g["params"]:
+                if id(p) in seen:
+                    continue
+                seen.add(id(p))
+                packs.setdefault((self._owner[id(p)], p.dtype, p.device), []).append(p)
+        for (owner, _dt, _dev), ps in packs.items():
+            if len(ps) == 1:
+                dist.broadcast(ps[0].data, src=self._global_rank(owner), group=self.process_group)
+                continue
+            flat = torch.cat([p.data.reshape(-1) for p in ps])
+            dist.broadcast(flat, src=self._global_rank(owner), group=self.process_group)
+            if owner != self.rank:
+                off = 0
+                for p in ps:
+                    n = p.numel()
+                    p.data.copy_(flat[off:off + n].view_as(p))
+                    off += n
+
+    def _global_rank(self, group_rank: int) -> int:
+        if self.process_group is None:
+            return group_rank
+        return dist.get_global_rank(self.process_group, group_rank)
+
+    # ------------------------------------------------------------------ NVLink fused path
+    def enable_symmetric(self, module: torch.nn.Module | None = None) -> bool:
+        """Move parameters into a symmetric arena and fuse AdamW + distribution (see module doc).
+        Returns False (and changes nothing) when the path is not legal for this setup."""
+        from . import symm_optimizer
+
+        s = symm_optimizer.try_make(self, module)
+        self._symm = s
+        return s is not None
+
+    # ------------------------------------------------------------------ checkpointing
+    def local_state_dict(self) -> dict:
+        return {} if self.optimizer is None else self.optimizer.state_dict()
+
+    def consolidated_state_dict(self, dst: int = 0) -> dict | None:
+        """Gather ``{param_index: state}`` for all parameters on ``dst`` (None elsewhere)."""
+        index = {}
+        i = 0
+        for g in self.param_groups:
+            for p in g["params"]:
+                index[id(p)] = i
+                i += 1
+        local = {}
+        if self.optimizer is not None:
+            for p, st in self.optimizer.state.items():
+                local[index[id(p)]] = {k: (v.detach().cpu() if torch.is_tensor(v) else v) for k, v in st.items()}
+        if self.world_size == 1:
+            return {"state": local, "owners": dict((index[k], v) for k, v in self._owner.items())}
+        gathered = [None] * self.world_size if self.rank == dst else None
+        dist.gather_object(local, gathered, dst=self._global_rank(dst), group=self.process_group)
+        if self.rank != dst:
+            return None
+        merged = {}
+        for d in gathered:
+            merged.update(d)
+        return {"state": merged, "owners": dict((index[k], v) for k, v in self._owner.items())}
+
+    def load_consolidated_state_dict(self, sd: dict) -> None:
+        """Inverse of :meth:`consolidated_state_dict`: every rank keeps only what it owns."""
+        if self.optimizer is None:
+            return
+        index = {}
+        i = 0
+        for g in self.param_groups:
+            for p in g["params"]:
+                index[i] = p
+                i += 1
+        for idx, st in sd["state"].items():
+            p = index[int(idx)]
+            if self._owner[id(p)] != self.rank:
+                continue
+            self.optimizer.state[p] = {k: (v.to(p.device) if torch.is_tensor(v) else v) for k, v in st.items()}

@@ -1,0 +1,79 @@
+"""FlashAttention-2 Functions vs. a materialised-softmax oracle (reference tests/test_attention.py)."""
+import pytest
+import torch
+
+from cs336_a2_systems_b200.ops.functional import attention_and_lse_ref
+
+from .adapters import (get_flashattention_autograd_function_pytorch,
+                       get_flashattention_autograd_function_triton)
+
+
+def _inputs(device, B=4, N=128, D=64, dtype=torch.float32, nk=None):
+    g = torch.Generator().manual_seed(0)
+    nk = nk or N
+    q = torch.randn(B, N, D, generator=g).to(device=device, dtype=dtype).requires_grad_(True)
+    k = torch.randn(B, nk, D, generator=g).to(device=device, dtype=dtype).requires_grad_(True)
+    v = torch.randn(B, nk, D, generator=g).to(device=device, dtype=dtype).requires_grad_(True)
+    do = torch.randn(B, N, D, generator=g).to(device=device, dtype=dtype)
+    return q, k, v, do
+
+
+def _check_forward(impl, device, is_causal, tol=1e-2, **kw):
+    q, k, v, _ = _inputs(device, **kw)
+    o = impl(q, k, v, is_causal)
+    o_ref, l_ref = attention_and_lse_ref(q, k, v, is_causal)
+    saved = [t for t in o.grad_fn.saved_tensors if t.shape == (q.shape[0], q.shape[1])]
+    assert len(saved) == 1, "exactly one saved tensor must have the logsumexp's shape (B, N_q)"
+    torch.testing.assert_close(o.float(), o_ref, rtol=tol, atol=tol)
+    torch.testing.assert_close(saved[0].float(), l_ref, rtol=tol, atol=tol)
+
+
+def _check_backward(impl, device, is_causal, tol=1e-2, **kw):
+    q, k, v, do = _inputs(device, **kw)
+    impl(q, k, v, is_causal).backward(do)
+    q2, k2, v2 = (t.detach().clone().requires_grad_(True) for t in (q, k, v))
+    attention_and_lse_ref(q2, k2, v2, is_causal)[0].backward(do.float())
+    for a, b in ((q, q2), (k, k2), (v, v2)):
+        torch.testing.assert_close(a.grad.float(), b.grad.float(), rtol=tol, atol=tol)
+
+
+@pytest.mark.parametrize("is_causal", [False, True])
+def test_flash_forward_pass_pytorch(is_causal):
+    _check_forward(get_flashattention_autograd_function_pytorch().apply, "cpu", is_causal)
+
+
+@pytest.mark.parametrize("is_causal", [False, True])
+def test_flash_backward_pytorch(is_causal):
+    _check_backward(get_flashattention_autograd_function_pytorch().apply, "cpu", is_causal)
+
+
+def test_flash_pytorch_ragged_and_2d():
+    """Sequence lengths that are not tile multiples, Nq != Nk, and un-batched (N, D) inputs."""
+    f = get_flashattention_autograd_function_pytorch().apply
+    _check_forward(f, "cpu", False, B=2, N=100, D=16, nk=75)
+    _check_backward(f, "cpu", False, B=2, N=100, D=16, nk=75)
+    q, k, v, _ = _inputs("cpu", B=1, N=48, D=32)
+    o = f(q[0], k[0], v[0], True)
+    o_ref, _ = attention_and_lse_ref(q, k, v, True)
+    torch.testing.assert_close(o, o_ref[0], rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("is_causal", [False, True])
+def test_flash_forward_pass_sm100(is_causal):
+    _check_forward(get_flashattention_autograd_function_triton().apply, "cuda", is_causal)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("is_causal", [False, True])
+def test_flash_backward_sm100(is_causal):
+    _check_backward(get_flashattention_autograd_function_triton().apply, "cuda", is_causal)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("N,D", [(128, 16), (256, 32), (512, 64), (1024, 128), (384, 80), (200, 64)])
+@pytest.mark.parametrize("is_causal", [False, True])
+def test_flash_sm100_shapes_bf16(N, D, is_causal):
+    f = get_flashattention_autograd_function_triton().apply
+    _check_forward(f, "cuda", is_causal, tol=2e-2, B=2, N=N, D=D, dtype=torch.bfloat16)
+    _check_backward(f, "cuda", is_causal, tol=3e-2, B=2, N=N, D=D, dtype=torch.bfloat16)
