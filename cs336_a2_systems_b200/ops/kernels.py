@@ -1,0 +1,357 @@
+"""ctypes bindings of ``libb200sys.so`` (see ``include/b200sys.h``).
+
+Thin, allocation-aware wrappers: they validate layouts, allocate outputs / scratch with torch
+(so the caching allocator and CUDA-graph private pools apply), pass raw device pointers and the
+current stream, and raise on any non-zero return code.  No autograd here — see ``native.py``.
+"""
+
+from __future__ import annotations
+
+import ctypes
+from ctypes import c_float, c_int, c_longlong, c_void_p
+
+import torch
+from torch import Tensor
+
+from .. import _native
+from .._native import check, p, stream_ptr
+
+BF16, F32 = 0, 1
+_DT = {torch.bfloat16: BF16, torch.float32: F32}
+
+EPI_BF16, EPI_F32, EPI_F32_ACC, EPI_BF16_SWIGLU, EPI_F32_RESID = 0, 1, 2, 3, 4
+
+#: launch counter (kernels launched through this module), for bench.py's "gpu_launches"
+launches = 0
+
+
+def _count(n: int = 1) -> None:
+    global launches
+    launches += n
+
+
+def _lib():
+    return _native.lib()
+
+
+# ------------------------------------------------------------------------------------------------
+# GEMM
+# ------------------------------------------------------------------------------------------------
+def gemm_supported(a: Tensor, b: Tensor) -> bool:
+    """TMA needs 16-byte aligned bases and row strides, unit inner stride."""
+    for t in (a, b):
+        if t.dtype != torch.bfloat16 or t.dim() != 2 or t.stride(1) != 1:
+            return False
+        if t.stride(0) % 8 != 0 or t.data_ptr() % 16 != 0:
+            return False
+    return True
+
+
+def gemm(a: Tensor, b: Tensor, *, a_mn: bool = False, b_mn: bool = False, epilogue: int = EPI_BF16,
+         out: Tensor | None = None, aux: Tensor | None = None, force_bn: int = 0) -> Tensor:
+    """``C = A · Bᵀ``.  ``a``: [M,K] (or [K,M] when ``a_mn``); ``b``: [N,K] (or [K,N] when ``b_mn``)."""
+    M, K = (a.shape[1], a.shape[0]) if a_mn else (a.shape[0], a.shape[1])
+    N, Kb = (b.shape[1], b.shape[0]) if b_mn else (b.shape[0], b.shape[1])
+    if K != Kb:
+        raise ValueError(f"gemm: inner dimensions differ ({K} vs {Kb})")
+    if not gemm_supported(a, b):
+        raise ValueError("gemm: operands must be bf16, 2-D, unit inner stride, 16-byte aligned rows")
+    n_out = N // 2 if epilogue == EPI_BF16_SWIGLU else N
+    if out is None:
+        dt = torch.bfloat16 if epilogue in (EPI_BF16, EPI_BF16_SWIGLU) else torch.float32
+        out = torch.empty(M, n_out, dtype=dt, device=a.device)
+    else:
+        assert out.shape == (M, n_out) and out.stride(1) == 1
+    ld_aux = aux.stride(0) if aux is not None else 0
+    check(_lib().b200_gemm_bf16(p(a), p(b), p(out), p(aux), c_int(M), c_int(N), c_int(K), c_int(a.stride(0)),
+                                c_int(b.stride(0)), c_int(out.stride(0)), c_int(ld_aux), c_int(int(a_mn)),
+                                c_int(int(b_mn)), c_int(epilogue), c_int(force_bn), stream_ptr()), "gemm")
+    _count()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# RMSNorm / residual
+# ------------------------------------------------------------------------------------------------
+def rmsnorm_fwd(x: Tensor, w: Tensor, eps: float, out_dtype: torch.dtype, resid: Tensor | None = None,
+                want_xout: bool = False):
+    """Returns ``(y, rstd, xout)``; with ``resid`` (bf16) the normalised value is ``x + resid``."""
+    d = x.shape[-1]
+    x2 = x.reshape(-1, d)
+    assert x2.is_contiguous() and w.dtype == torch.float32 and w.is_contiguous()
+    T = x2.shape[0]
+    y = torch.empty(x.shape, dtype=out_dtype, device=x.device)
+    rstd = torch.empty(T, dtype=torch.float32, device=x.device)
+    xout = torch.empty(x.shape, dtype=torch.float32, device=x.device) if (want_xout or resid is not None) else None
+    if resid is not None:
+        assert resid.dtype == torch.bfloat16 and resid.is_contiguous() and resid.numel() == x.numel()
+    check(_lib().b200_rmsnorm_fwd(p(x2), c_int(_DT[x.dtype]), p(resid), p(w), p(y), c_int(_DT[out_dtype]), p(xout),
+                                  p(rstd), c_int(T), c_int(d), c_float(eps), stream_ptr()), "rmsnorm_fwd")
+    _count()
+    return y, rstd, xout
+
+
+def rmsnorm_bwd(dy: Tensor, x: Tensor, w: Tensor, rstd: Tensor, dres_in: Tensor | None, want_dx_bf16: bool,
+                dw_out: Tensor | None = None, want_dx_f32: bool = True):
+    """``x`` is the fp32 tensor that was normalised.  Returns ``(dx_f32, dx_bf16, dw)``."""
+    d = x.shape[-1]
+    T = x.numel() // d
+    assert x.dtype == torch.float32 and x.is_contiguous() and dy.is_contiguous()
+    dx = torch.empty_like(x) if want_dx_f32 else None
+    dxb = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device) if want_dx_bf16 else None
+    dw = dw_out if dw_out is not None else torch.empty_like(w)
+    rows = _lib().b200_rmsnorm_bwd_workspace_rows(c_int(T))
+    scratch = torch.empty(rows * d, dtype=torch.float32, device=x.device)
+    check(_lib().b200_rmsnorm_bwd(p(dy), c_int(_DT[dy.dtype]), p(x), p(w), p(rstd), p(dres_in), p(dx), p(dxb), p(dw),
+                                  c_int(0), p(scratch), c_int(T), c_int(d), stream_ptr()), "rmsnorm_bwd")
+    _count(2)
+    return dx, dxb, dw
+
+
+def residual_add(x: Tensor, y: Tensor) -> Tensor:
+    assert x.dtype == torch.float32 and y.dtype == torch.bfloat16 and x.is_contiguous() and y.is_contiguous()
+    out = torch.empty_like(x)
+    check(_lib().b200_residual_add(p(x), p(y), p(out), c_longlong(x.numel()), stream_ptr()), "residual_add")
+    _count()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# RoPE / SwiGLU / embedding / cast
+# ------------------------------------------------------------------------------------------------
+def rope_qk_inplace(qkv: Tensor, cache: Tensor, inverse: bool = False) -> None:
+    """``qkv``: contiguous bf16 ``[B, S, 3, H, dh]``; rotates q and k in place."""
+    B, S, three, H, dh = qkv.shape
+    assert three == 3 and qkv.is_contiguous() and qkv.dtype == torch.bfloat16
+    assert cache.dtype == torch.float32 and cache.is_contiguous() and cache.shape[2] == dh // 2
+    check(_lib().b200_rope_qk_inplace(p(qkv), p(cache), c_int(cache.shape[1]), c_int(B), c_int(S), c_int(H),
+                                      c_int(dh), c_int(int(inverse)), stream_ptr()), "rope")
+    _count()
+
+
+def swiglu_fwd(ab: Tensor) -> Tensor:
+    F = ab.shape[-1] // 2
+    assert ab.is_contiguous() and ab.dtype == torch.bfloat16
+    g = torch.empty(ab.shape[:-1] + (F,), dtype=torch.bfloat16, device=ab.device)
+    check(_lib().b200_swiglu_fwd(p(ab), p(g), c_longlong(ab.numel() // (2 * F)), c_int(F), stream_ptr()), "swiglu_fwd")
+    _count()
+    return g
+
+
+def swiglu_bwd(ab: Tensor, dg: Tensor) -> Tensor:
+    F = ab.shape[-1] // 2
+    dg = dg.contiguous()
+    dab = torch.empty_like(ab)
+    check(_lib().b200_swiglu_bwd(p(ab), p(dg), p(dab), c_longlong(ab.numel() // (2 * F)), c_int(F), stream_ptr()),
+          "swiglu_bwd")
+    _count()
+    return dab
+
+
+def embedding_fwd(ids: Tensor, w: Tensor) -> Tensor:
+    assert ids.dtype == torch.int64 and w.dtype == torch.float32 and w.is_contiguous()
+    idc = ids.contiguous()
+    out = torch.empty(ids.shape + (w.shape[1],), dtype=torch.float32, device=w.device)
+    check(_lib().b200_embedding_fwd(p(idc), p(w), p(out), c_longlong(idc.numel()), c_int(w.shape[1]),
+                                    c_int(w.shape[0]), stream_ptr()), "embedding_fwd")
+    _count()
+    return out
+
+
+def embedding_bwd(ids: Tensor, dout: Tensor, dw: Tensor, zero_first: bool = True) -> Tensor:
+    idc = ids.contiguous()
+    dout = dout.contiguous()
+    assert dout.dtype == torch.float32 and dw.dtype == torch.float32 and dw.is_contiguous()
+    check(_lib().b200_embedding_bwd(p(idc), p(dout), p(dw), c_longlong(idc.numel()), c_int(dw.shape[1]),
+                                    c_int(dw.shape[0]), c_int(int(zero_first)), stream_ptr()), "embedding_bwd")
+    _count(2 if zero_first else 1)
+    return dw
+
+
+def cast_bf16(src: Tensor, out: Tensor | None = None) -> Tensor:
+    assert src.dtype == torch.float32 and src.is_contiguous()
+    if out is None:
+        out = torch.empty(src.shape, dtype=torch.bfloat16, device=src.device)
+    assert out.is_contiguous() and out.numel() == src.numel()
+    check(_lib().b200_cast_f32_to_bf16(p(src), p(out), c_longlong(src.numel()), stream_ptr()), "cast")
+    _count()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# cross-entropy
+# ------------------------------------------------------------------------------------------------
+def xent_fwd(logits2d: Tensor, targets: Tensor):
+    T, V = logits2d.shape
+    assert logits2d.stride(1) == 1 and targets.dtype == torch.int64 and targets.is_contiguous()
+    row_loss = torch.empty(T, dtype=torch.float32, device=logits2d.device)
+    lse = torch.empty(T, dtype=torch.float32, device=logits2d.device)
+    loss = torch.empty((), dtype=torch.float32, device=logits2d.device)
+    check(_lib().b200_xent_fwd(p(logits2d), c_int(_DT[logits2d.dtype]), p(targets), p(row_loss), p(lse), p(loss),
+                               c_int(T), c_int(V), c_int(logits2d.stride(0)), stream_ptr()), "xent_fwd")
+    _count(2)
+    return loss, lse
+
+
+def xent_bwd(logits2d: Tensor, targets: Tensor, lse: Tensor, dloss: Tensor, out: Tensor | None = None) -> Tensor:
+    T, V = logits2d.shape
+    if out is None:
+        out = torch.empty_like(logits2d)
+    dloss = dloss.to(torch.float32).contiguous()
+    check(_lib().b200_xent_bwd(p(logits2d), c_int(_DT[logits2d.dtype]), p(targets), p(lse), p(dloss), p(out),
+                               c_int(T), c_int(V), c_int(logits2d.stride(0)), c_int(out.stride(0)), stream_ptr()),
+          "xent_bwd")
+    _count()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# multi-tensor AdamW / clipping
+# ------------------------------------------------------------------------------------------------
+class _AdamWTensor(ctypes.Structure):
+    _fields_ = [("p", c_void_p), ("g", c_void_p), ("m", c_void_p), ("v", c_void_p), ("shadow", c_void_p),
+                ("n", c_longlong), ("aligned16", c_int), ("pad_", c_int)]
+
+
+class TensorTable:
+    """Device-resident descriptor table over a list of (param, grad, m, v, shadow) tensors."""
+
+    def __init__(self, params, grads, ms=None, vs=None, shadows=None):
+        n = len(params)
+        chunk = _lib().b200_adamw_chunk_elems()
+        arr = (_AdamWTensor * n)()
+        starts = []
+        total = 0
+        for i in range(n):
+            ptrs = [params[i].data_ptr() if params[i] is not None else 0,
+                    grads[i].data_ptr() if grads[i] is not None else 0,
+                    ms[i].data_ptr() if ms is not None else 0,
+                    vs[i].data_ptr() if vs is not None else 0]
+            sh = shadows[i] if shadows is not None else None
+            numel = (grads[i] if grads[i] is not None else params[i]).numel()
+            arr[i].p, arr[i].g, arr[i].m, arr[i].v = ptrs
+            arr[i].shadow = sh.data_ptr() if sh is not None else 0
+            arr[i].n = numel
+            al = all(q % 16 == 0 for q in ptrs) and (sh is None or sh.data_ptr() % 8 == 0)
+            arr[i].aligned16 = int(al)
+            starts.append(total)
+            total += (numel + chunk - 1) // chunk
+        dev = (grads[0] if grads[0] is not None else params[0]).device
+        raw = bytes(arr)
+        self.table = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(dev)
+        self.starts = torch.tensor(starts, dtype=torch.int64).to(dev)
+        self.n = n
+        self.total_chunks = total
+        self.device = dev
+
+
+class AdamWLaunch:
+    """Holds the table, device hyper-parameters and the device step counter of one fused group."""
+
+    def __init__(self, params, grads, ms, vs, shadows, step0: int, mode: int = 0):
+        self.tt = TensorTable(params, grads, ms, vs, shadows)
+        dev = self.tt.device
+        self.hyper = torch.zeros(8, dtype=torch.float32, device=dev)
+        # ring of pinned staging rows: the host may run several steps ahead of the async copies
+        self._hyper_host = torch.zeros(16, 8, dtype=torch.float32).pin_memory()
+        self._hyper_slot = 0
+        self._hyper_vals = None
+        self.step = torch.tensor([step0], dtype=torch.int32, device=dev)
+        self.mode = mode
+
+    def set_hyper(self, lr, b1, b2, eps, wd, grad_scale=1.0) -> None:
+        vals = (float(lr), float(b1), float(b2), float(eps), float(wd), float(grad_scale))
+        if vals == self._hyper_vals:
+            return
+        self._hyper_vals = vals
+        row = self._hyper_host[self._hyper_slot]
+        self._hyper_slot = (self._hyper_slot + 1) % self._hyper_host.shape[0]
+        row[:6] = torch.tensor(vals, dtype=torch.float32)
+        self.hyper.copy_(row, non_blocking=True)
+
+    def launch(self) -> None:
+        check(_lib().b200_adamw_multi(p(self.tt.table), p(self.tt.starts), c_int(self.tt.n),
+                                      c_longlong(self.tt.total_chunks), p(self.hyper), p(self.step),
+                                      c_int(self.mode), c_int(1), stream_ptr()), "adamw_multi")
+        _count(2)
+
+
+def clip_grad_norm(grads: list[Tensor], max_norm: float, eps: float, table: TensorTable | None = None) -> Tensor:
+    tt = table or TensorTable([None] * len(grads), grads)
+    nparts = _lib().b200_gradnorm_partials(c_longlong(tt.total_chunks))
+    partial = torch.empty(nparts, dtype=torch.float32, device=tt.device)
+    out = torch.empty(2, dtype=torch.float32, device=tt.device)
+    check(_lib().b200_clip_grad_norm(p(tt.table), p(tt.starts), c_int(tt.n), c_longlong(tt.total_chunks),
+                                     c_float(max_norm), c_float(eps), p(partial), p(out), c_int(1), stream_ptr()),
+          "clip_grad_norm")
+    _count(3)
+    return out[0]
+
+
+# ------------------------------------------------------------------------------------------------
+# FlashAttention-2
+# ------------------------------------------------------------------------------------------------
+def _strides3(t: Tensor):
+    assert t.dim() == 4 and t.stride(3) == 1, "attention operands are (B, H, N, D) views with unit inner stride"
+    return (c_longlong * 3)(t.stride(0), t.stride(1), t.stride(2))
+
+
+def fa2_fwd(q: Tensor, k: Tensor, v: Tensor, causal: bool, out: Tensor | None = None):
+    """``q,k,v``: bf16 ``(B, H, N, D)`` views (any batch/head/row strides).  Returns ``(o, lse)``;
+    ``o`` has q's layout unless ``out`` is given, ``lse`` is fp32 ``(B, H, Nq)``."""
+    B, H, Nq, D = q.shape
+    Nk = k.shape[2]
+    assert q.dtype == k.dtype == v.dtype == torch.bfloat16
+    if out is None:
+        out = torch.empty_strided(q.shape, q.stride(), dtype=torch.bfloat16, device=q.device) \
+            if q.is_contiguous() else torch.empty(B, Nq, H, D, dtype=torch.bfloat16, device=q.device).permute(0, 2, 1, 3)
+    lse = torch.empty(B, H, Nq, dtype=torch.float32, device=q.device)
+    check(_lib().b200_fa2_fwd(p(q), p(k), p(v), p(out), p(lse), c_int(B), c_int(H), c_int(Nq), c_int(Nk), c_int(D),
+                              _strides3(q), _strides3(k), _strides3(v), _strides3(out), c_int(int(causal)),
+                              c_float(1.0 / (D ** 0.5)), stream_ptr()), "fa2_fwd")
+    _count()
+    return out, lse
+
+
+def fa2_bwd(q, k, v, o, lse, do, causal: bool, dq=None, dk=None, dv=None):
+    B, H, Nq, D = q.shape
+    Nk = k.shape[2]
+    if do.stride(3) != 1:
+        do = do.contiguous()
+    dq = torch.empty_like(q) if dq is None else dq
+    dk = torch.empty_like(k) if dk is None else dk
+    dv = torch.empty_like(v) if dv is None else dv
+    delta = torch.empty(B, H, Nq, dtype=torch.float32, device=q.device)
+    dq_acc = torch.empty(B, H, Nq, D, dtype=torch.float32, device=q.device)
+    check(_lib().b200_fa2_bwd(p(q), p(k), p(v), p(o), p(lse), p(do), p(dq), p(dk), p(dv), p(delta), p(dq_acc),
+                              c_int(B), c_int(H), c_int(Nq), c_int(Nk), c_int(D), _strides3(q), _strides3(k),
+                              _strides3(v), _strides3(o), _strides3(do), _strides3(dq), _strides3(dk), _strides3(dv),
+                              c_int(int(causal)), c_float(1.0 / (D ** 0.5)), stream_ptr()), "fa2_bwd")
+    _count(4)
+    return dq, dk, dv
+
+
+# ------------------------------------------------------------------------------------------------
+# NVLink collectives
+# ------------------------------------------------------------------------------------------------
+_signal_slot = 0
+
+
+def allreduce_avg(arena, byte_off: int, numel: int, dtype: torch.dtype, one_shot_max: int, blocks: int,
+                  algo: int = 0) -> None:
+    """In-place average over ranks of ``numel`` elements at ``byte_off`` of the symmetric arena."""
+    global _signal_slot
+    es = 2 if dtype == torch.bfloat16 else 4
+    if algo == 0:
+        if numel * es <= one_shot_max:
+            algo = 1
+        elif arena.multicast_ptr:
+            algo = 3
+        else:
+            algo = 2
+    check(_lib().b200_allreduce(c_void_p(arena.peer_ptrs_dev), c_void_p(arena.signal_ptrs_dev),
+                                c_void_p(arena.multicast_ptr), c_longlong(byte_off), c_longlong(numel),
+                                c_int(_DT[dtype]), c_float(1.0 / arena.world_size), c_int(arena.rank),
+                                c_int(arena.world_size), c_int(algo), c_int(blocks), c_int(0), stream_ptr()),
+          "allreduce")
+    _count()

@@ -1,0 +1,362 @@
+"""Autograd wrappers around the sm_100a kernels, and the bf16 weight-shadow registry.
+
+Design notes
+------------
+* **Weight shadows.**  Parameters stay fp32 (master weights, exactly like the reference under
+  ``torch.autocast``), the tcgen05 GEMMs read bf16 copies.  A shadow is cached per *group* of
+  weights that are applied to the same input (q/k/v, w1/w3 → one concatenated ``[ΣN, K]``
+  buffer → ONE GEMM) and is refreshed only when a member's ``_version`` changed; the fused
+  AdamW kernel writes the shadows itself, so in steady state no cast kernel runs at all.
+* **Gradient destinations.**  Weight gradients are produced straight into the slot registered in
+  ``grad_slots`` (a DDP bucket in NVLink symmetric memory or a flat optimizer arena) by the wgrad
+  GEMM epilogue; autograd adopts the returned view as ``.grad`` without copying.
+* Every Function here has a plain-PyTorch oracle in ``functional.py``; ``tests/test_kernels_gpu.py``
+  compares them.
+"""
+
+from __future__ import annotations
+
+import torch
+from torch import Tensor
+
+from . import grad_slots, kernels
+
+BF16 = torch.bfloat16
+
+
+# ------------------------------------------------------------------------------------------------
+# weight shadows
+# ------------------------------------------------------------------------------------------------
+class _ShadowEntry:
+    __slots__ = ("tensor", "versions", "row_offsets")
+
+    def __init__(self, tensor, versions, row_offsets):
+        self.tensor, self.versions, self.row_offsets = tensor, versions, row_offsets
+
+
+def _shadow_entry(weights: tuple[Tensor, ...]) -> _ShadowEntry:
+    key = tuple(id(w) for w in weights)
+    w0 = weights[0]
+    reg = getattr(w0, "_b200_shadows", None)
+    if reg is None:
+        reg = {}
+        w0._b200_shadows = reg
+    ent = reg.get(key)
+    if ent is None:
+        K = w0.shape[1]
+        offs, n = [], 0
+        for w in weights:
+            assert w.dim() == 2 and w.shape[1] == K and w.dtype == torch.float32
+            offs.append(n)
+            n += w.shape[0]
+        ent = _ShadowEntry(torch.empty(n, K, dtype=BF16, device=w0.device), [None] * len(weights), offs)
+        reg[key] = ent
+        for i, w in enumerate(weights):  # let the optimizer find the slice it must keep fresh
+            lst = getattr(w, "_b200_shadow_slices", None)
+            if lst is None:
+                lst = []
+                w._b200_shadow_slices = lst
+            lst.append((ent, i))
+    return ent
+
+
+def weight_shadow(weights: tuple[Tensor, ...]) -> Tensor:
+    """bf16 ``[ΣN, K]`` concatenation of the group's weights, refreshed if any member changed."""
+    ent = _shadow_entry(weights)
+    for i, w in enumerate(weights):
+        if ent.versions[i] != w._version or ent.tensor.device != w.device:
+            if ent.tensor.device != w.device:
+                ent.tensor = torch.empty_like(ent.tensor, device=w.device)
+                ent.versions = [None] * len(weights)
+            r0 = ent.row_offsets[i]
+            dst = ent.tensor[r0:r0 + w.shape[0]]
+            src = w.detach()
+            if src.is_contiguous():
+                kernels.cast_bf16(src, dst)
+            else:
+                dst.copy_(src)
+            ent.versions[i] = w._version
+    return ent.tensor
+
+
+def shadow_slices_of(w: Tensor) -> list[Tensor]:
+    """bf16 views that mirror parameter ``w`` (for the fused optimizer to refresh in its own pass)."""
+    out = []
+    for ent, i in getattr(w, "_b200_shadow_slices", []):
+        if ent.tensor.device == w.device and ent.versions[i] == w._version:
+            r0 = ent.row_offsets[i]
+            out.append(ent.tensor[r0:r0 + w.shape[0]])
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# linear
+# ------------------------------------------------------------------------------------------------
+def _to_bf16_2d(x: Tensor, K: int) -> Tensor:
+    x2 = x.reshape(-1, K)
+    if x2.dtype == torch.float32:
+        return kernels.cast_bf16(x2.contiguous())
+    if x2.dtype != BF16:
+        x2 = x2.to(BF16)
+    if x2.stride(1) != 1 or x2.stride(0) % 8 != 0 or x2.data_ptr() % 16 != 0:
+        x2 = x2.contiguous()
+    return x2
+
+
+class LinearFn(torch.autograd.Function):
+    """``y = x · [W_0; W_1; …]ᵀ`` on the tcgen05 GEMM; backward = dgrad (NN) + one wgrad (TN) per weight."""
+
+    @staticmethod
+    def forward(ctx, x: Tensor, wb: Tensor, *weights: Tensor):
+        N, K = wb.shape
+        x2 = _to_bf16_2d(x, K)
+        y = kernels.gemm(x2, wb)
+        ctx.save_for_backward(x2, wb)
+        ctx.weights = weights
+        ctx.x_shape = x.shape
+        ctx.x_dtype = x.dtype
+        return y.view(*x.shape[:-1], N)
+
+    @staticmethod
+    def backward(ctx, dy: Tensor):
+        x2, wb = ctx.saved_tensors
+        N, K = wb.shape
+        dy2 = _to_bf16_2d(dy, N)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = kernels.gemm(dy2, wb, b_mn=True)  # [T,N]·[N,K]
+            dx = dx.view(ctx.x_shape)
+            if ctx.x_dtype != BF16:
+                dx = dx.to(ctx.x_dtype)
+        dws = []
+        r0 = 0
+        for i, w in enumerate(ctx.weights):
+            n_i = w.shape[0]
+            if ctx.needs_input_grad[2 + i]:
+                dst = grad_slots.claim(w)
+                dyi = dy2[:, r0:r0 + n_i]  # column slice: MN-major A operand with lda = N
+                if dyi.data_ptr() % 16 != 0:
+                    dyi = dyi.contiguous()
+                dws.append(kernels.gemm(dyi, x2, a_mn=True, b_mn=True, epilogue=kernels.EPI_F32, out=dst))
+            else:
+                dws.append(None)
+            r0 += n_i
+        return (dx, None, *dws)
+
+
+def linear(x: Tensor, weights: tuple[Tensor, ...]) -> Tensor:
+    """Apply one or several bias-free linear maps that share the input (outputs concatenated)."""
+    wb = weight_shadow(weights)
+    return LinearFn.apply(x, wb, *weights)
+
+
+# ------------------------------------------------------------------------------------------------
+# RMSNorm (+ residual)
+# ------------------------------------------------------------------------------------------------
+class RMSNormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x: Tensor, w: Tensor, eps: float, out_dtype: torch.dtype):
+        xc = x.contiguous()
+        y, rstd, _ = kernels.rmsnorm_fwd(xc, w.detach(), eps, out_dtype)
+        ctx.save_for_backward(xc, w, rstd)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy: Tensor):
+        x, w, rstd = ctx.saved_tensors
+        xf = x if x.dtype == torch.float32 else x.float()
+        dst = grad_slots.claim(w) if ctx.needs_input_grad[1] else None
+        dx, _, dw = kernels.rmsnorm_bwd(dy.contiguous(), xf, w.detach(), rstd, None, False, dw_out=dst)
+        if x.dtype != torch.float32:
+            dx = dx.to(x.dtype)
+        return dx, (dw if ctx.needs_input_grad[1] else None), None, None
+
+
+def rmsnorm(x: Tensor, w: Tensor, eps: float, out_dtype: torch.dtype) -> Tensor:
+    return RMSNormFn.apply(x, w, eps, out_dtype)
+
+
+class AddRMSNormFn(torch.autograd.Function):
+    """``x' = x + y`` (fp32 residual stream + bf16 branch), ``h = rmsnorm(x')·w`` in bf16 — one kernel.
+    Backward merges the residual-path gradient with the norm gradient and emits both the fp32
+    stream gradient and its bf16 copy for the branch in one pass."""
+
+    @staticmethod
+    def forward(ctx, x: Tensor, y: Tensor, w: Tensor, eps: float):
+        ctx.set_materialize_grads(False)
+        h, rstd, xout = kernels.rmsnorm_fwd(x.contiguous(), w.detach(), eps, BF16, resid=y.contiguous())
+        ctx.save_for_backward(xout, w, rstd)
+        return xout, h
+
+    @staticmethod
+    def backward(ctx, dxout: Tensor | None, dh: Tensor | None):
+        xout, w, rstd = ctx.saved_tensors
+        if dh is None:
+            if dxout is None:
+                return None, None, None, None
+            return dxout, dxout.to(BF16), None, None
+        dst = grad_slots.claim(w) if ctx.needs_input_grad[2] else None
+        dres = dxout.contiguous() if dxout is not None else None
+        dx, dxb, dw = kernels.rmsnorm_bwd(dh.contiguous(), xout, w.detach(), rstd, dres, True, dw_out=dst)
+        return dx, dxb, (dw if ctx.needs_input_grad[2] else None), None
+
+
+def add_rmsnorm(x: Tensor, y: Tensor, w: Tensor, eps: float):
+    return AddRMSNormFn.apply(x, y, w, eps)
+
+
+class ResidualAddFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x: Tensor, y: Tensor):
+        return kernels.residual_add(x.contiguous(), y.contiguous())
+
+    @staticmethod
+    def backward(ctx, g: Tensor):
+        return g, g.to(BF16)
+
+
+def residual_add(x: Tensor, y: Tensor) -> Tensor:
+    return ResidualAddFn.apply(x, y)
+
+
+# ------------------------------------------------------------------------------------------------
+# attention core: RoPE (in place) + FlashAttention-2
+# ------------------------------------------------------------------------------------------------
+class AttentionCoreFn(torch.autograd.Function):
+    """``qkv``: bf16 ``[B, S, 3, H, dh]`` straight from the fused QKV GEMM.  Rotates q,k in place
+    (nothing else reads the un-rotated values), runs causal FA2 on strided views (no head
+    transposes), returns ``[B, S, H·dh]``.  Backward writes dq/dk/dv into one ``[B,S,3,H,dh]``
+    buffer and un-rotates dq,dk in place — ready to be the dgrad/wgrad GEMM operand."""
+
+    @staticmethod
+    def forward(ctx, qkv: Tensor, rope_cache: Tensor):
+        B, S, _, H, dh = qkv.shape
+        assert qkv.is_contiguous()
+        kernels.rope_qk_inplace(qkv, rope_cache)
+        q, k, v = (qkv[:, :, i].permute(0, 2, 1, 3) for i in range(3))  # (B, H, S, dh) strided views
+        o = torch.empty(B, S, H, dh, dtype=BF16, device=qkv.device)
+        _, lse = kernels.fa2_fwd(q, k, v, True, out=o.permute(0, 2, 1, 3))
+        ctx.save_for_backward(qkv, o, lse, rope_cache)
+        return o.view(B, S, H * dh)
+
+    @staticmethod
+    def backward(ctx, do: Tensor):
+        qkv, o, lse, rope_cache = ctx.saved_tensors
+        B, S, _, H, dh = qkv.shape
+        q, k, v = (qkv[:, :, i].permute(0, 2, 1, 3) for i in range(3))
+        dqkv = torch.empty_like(qkv)
+        dq, dk, dv = (dqkv[:, :, i].permute(0, 2, 1, 3) for i in range(3))
+        do4 = do.contiguous().view(B, S, H, dh).permute(0, 2, 1, 3)
+        kernels.fa2_bwd(q, k, v, o.permute(0, 2, 1, 3), lse, do4, True, dq=dq, dk=dk, dv=dv)
+        kernels.rope_qk_inplace(dqkv, rope_cache, inverse=True)
+        return dqkv, None
+
+
+def attention_core(qkv: Tensor, rope_cache: Tensor) -> Tensor:
+    return AttentionCoreFn.apply(qkv, rope_cache)
+
+
+# ------------------------------------------------------------------------------------------------
+# SwiGLU gate, embedding, cross-entropy
+# ------------------------------------------------------------------------------------------------
+class SwiGLUFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, ab: Tensor):
+        abc = ab.contiguous()
+        ctx.save_for_backward(abc)
+        return kernels.swiglu_fwd(abc)
+
+    @staticmethod
+    def backward(ctx, dg: Tensor):
+        (ab,) = ctx.saved_tensors
+        return kernels.swiglu_bwd(ab, dg)
+
+
+def swiglu(ab: Tensor) -> Tensor:
+    return SwiGLUFn.apply(ab)
+
+
+class EmbeddingFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, ids: Tensor, w: Tensor):
+        ctx.save_for_backward(ids)
+        ctx.w = w
+        return kernels.embedding_fwd(ids, w.detach())
+
+    @staticmethod
+    def backward(ctx, dout: Tensor):
+        (ids,) = ctx.saved_tensors
+        w = ctx.w
+        dst = grad_slots.claim(w)
+        if dst is None:
+            dst = torch.empty_like(w)
+        kernels.embedding_bwd(ids, dout.float() if dout.dtype != torch.float32 else dout, dst, zero_first=True)
+        return None, dst
+
+
+def embedding(ids: Tensor, w: Tensor) -> Tensor:
+    return EmbeddingFn.apply(ids, w)
+
+
+class CrossEntropyFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits: Tensor, targets: Tensor):
+        V = logits.shape[-1]
+        l2 = logits.reshape(-1, V)
+        if l2.stride(1) != 1:
+            l2 = l2.contiguous()
+        t = targets.reshape(-1).contiguous()
+        loss, lse = kernels.xent_fwd(l2, t)
+        ctx.save_for_backward(l2, t, lse)
+        ctx.shape = logits.shape
+        return loss
+
+    @staticmethod
+    def backward(ctx, dloss: Tensor):
+        l2, t, lse = ctx.saved_tensors
+        return kernels.xent_bwd(l2, t, lse, dloss).view(ctx.shape), None
+
+
+def cross_entropy(logits: Tensor, targets: Tensor) -> Tensor:
+    return CrossEntropyFn.apply(logits, targets)
+
+
+# ------------------------------------------------------------------------------------------------
+# optimizer-side helpers
+# ------------------------------------------------------------------------------------------------
+def clip_grad_norm_(grads: list[Tensor], max_norm: float, eps: float = 1e-6) -> Tensor:
+    return kernels.clip_grad_norm([g.contiguous() if not g.is_contiguous() else g for g in grads], max_norm, eps)
+
+
+class AdamWPlan:
+    """One fused launch over a fixed set of (param, grad, m, v) tensors (+ their bf16 shadows)."""
+
+    def __init__(self, params, grads, ms, vs, key, step0: int, mode: int = 0):
+        self.key = key
+        self.params = list(params)
+        flat_p, flat_g, flat_m, flat_v, flat_s = [], [], [], [], []
+        self._extra_shadows = []
+        for p_, g_, m_, v_ in zip(params, grads, ms, vs):
+            sl = shadow_slices_of(p_)
+            flat_p.append(p_.data)
+            flat_g.append(g_)
+            flat_m.append(m_)
+            flat_v.append(v_)
+            first = sl[0] if sl else None
+            if first is not None and not first.is_contiguous():
+                first = None
+            flat_s.append(first)
+            for extra in sl[1:]:
+                self._extra_shadows.append((p_, extra))
+        self._launch = kernels.AdamWLaunch(flat_p, flat_g, flat_m, flat_v, flat_s, step0, mode)
+
+    def set_hyper(self, lr, b1, b2, eps, wd, grad_scale: float = 1.0) -> None:
+        self._launch.set_hyper(lr, b1, b2, eps, wd, grad_scale)
+
+    def launch(self) -> None:
+        self._launch.launch()
+        for p_, sh in self._extra_shadows:  # a weight mirrored in several groups (rare)
+            kernels.cast_bf16(p_.data, sh)
+
+    def device_step(self) -> int:
+        return int(self._launch.step.item())

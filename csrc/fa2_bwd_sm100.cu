@@ -1,0 +1,437 @@
+// FlashAttention-2 backward on tcgen05 / TMEM / TMA for sm_100a.
+//
+// The reference backward (cs336_systems/flash_attention.py:270-289) is a torch.compile'd graph
+// that materialises the full N×N S, P, dP and dS matrices (O(N²) memory).  This is the tiled
+// algorithm (FlashAttention-2, Algorithm 2): P is recomputed from the saved logsumexp tile by
+// tile, nothing N×N ever reaches HBM.
+//
+//   pre-pass   delta = rowsum(O ∘ dO)                                   (fa2_delta_kernel)
+//   main       one CTA per 128-key tile j of one (batch, head); loop over query tiles i:
+//                S  = Q_i·K_jᵀ          dP = dO_i·V_jᵀ                     (tcgen05, both K-major)
+//                P  = exp2(S·c − L_i)    dS = P ∘ (dP − delta_i)·scale      (softmax warpgroup, TMEM→regs→smem)
+//                dV_j += Pᵀ·dO_i        dK_j += dSᵀ·Q_i                    (A read MN-major from the same smem tile)
+//                dQ_i += dS·K_j                                            (partial in TMEM → fp32 red.add.v4 to HBM)
+//              dK_j, dV_j stay in tensor memory for the whole loop.
+//   post-pass  dQ fp32 accumulator → bf16                                (fa2_dq_convert_kernel)
+#include "common.cuh"
+#include "ptx.cuh"
+#include "tensormap.h"
+
+namespace b200 {
+namespace fa2 {
+
+constexpr int BM = 128;
+constexpr int BN = 128;
+constexpr int kThreads = 192;
+constexpr float kLog2e = 1.4426950408889634f;
+
+int make_bhnd_map(CUtensorMap* out, const void* base, int B, int H, int N, int D, const long long* strides,
+                  int box_rows);
+
+template <int DP>
+struct BwdCfg {
+  static constexpr int NBLK = DP / 64;
+  static constexpr int TILE_BYTES = 128 * DP * 2;
+  static constexpr int PS_BYTES = BM * BN * 2;
+  static constexpr int STAGES = DP == 64 ? 2 : 1;
+  static constexpr bool ALIAS = DP != 64;  // dQ partial shares S's TMEM columns when DP = 128
+  static constexpr int SMEM_BYTES = 2 * TILE_BYTES + STAGES * 2 * TILE_BYTES + 2 * PS_BYTES + 1024 + 256;
+  static constexpr int COL_S = 0, COL_DP = 128, COL_DV = 256, COL_DK = 256 + DP;
+  static constexpr int COL_DQ = ALIAS ? 0 : 256 + 2 * DP;
+  static constexpr int TMEM_COLS = 512;
+};
+
+struct BwdParams {
+  const float* lse;
+  const float* delta;
+  float* dq_acc;  // [B,H,Nq,D] fp32, zeroed
+  __nv_bfloat16 *dk, *dv;
+  long long dk_sb, dk_sh, dk_sr, dv_sb, dv_sh, dv_sr;
+  int H, Nq, Nk, D;
+  int causal;
+  float scale, scale_log2;
+  int num_q_tiles;
+};
+
+__device__ __forceinline__ uint32_t swz_off_b(int row, int col, int rows) {
+  const int blk = col >> 6, c = col & 63;
+  return blk * (rows * 128) + row * 128 + ((((c >> 3) ^ (row & 7)) << 4) | ((c & 7) << 1));
+}
+
+template <int DP>
+__global__ void __launch_bounds__(kThreads, 1)
+fa2_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+               const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO, const BwdParams p) {
+  using C = BwdCfg<DP>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sK = smem;
+  uint8_t* sV = sK + C::TILE_BYTES;
+  uint8_t* sStage = sV + C::TILE_BYTES;  // per stage: Q_i then dO_i
+  uint8_t* sP = sStage + C::STAGES * 2 * C::TILE_BYTES;
+  uint8_t* sdS = sP + C::PS_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sdS + C::PS_BYTES);
+  uint64_t* kv_full = bars;
+  uint64_t* qdo_full = bars + 1;
+  uint64_t* qdo_empty = qdo_full + C::STAGES;
+  uint64_t* sdp_full = qdo_empty + C::STAGES;
+  uint64_t* pds_full = sdp_full + 1;
+  uint64_t* dq_full = pds_full + 1;
+  uint64_t* dq_empty = dq_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(dq_empty + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int j = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int kv0 = j * BN;
+  const int i_start = p.causal ? (kv0 / BM) : 0;
+  const int n_iter = max(0, p.num_q_tiles - i_start);
+
+  if (warp == 4 && ptx::elect_one()) {
+    ptx::tma_prefetch_desc(&tmQ);
+    ptx::tma_prefetch_desc(&tmK);
+    ptx::tma_prefetch_desc(&tmV);
+    ptx::tma_prefetch_desc(&tmdO);
+    ptx::mbar_init(kv_full, 1);
+    for (int s = 0; s < C::STAGES; ++s) {
+      ptx::mbar_init(&qdo_full[s], 1);
+      ptx::mbar_init(&qdo_empty[s], 1);
+    }
+    ptx::mbar_init(sdp_full, 1);
+    ptx::mbar_init(pds_full, 4);
+    ptx::mbar_init(dq_full, 1);
+    ptx::mbar_init(dq_empty, 4);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 5) {
+    ptx::tmem_alloc(tmem_slot, C::TMEM_COLS);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 4) {
+    // ===================================== TMA producer =====================================
+    if (ptx::elect_one() && n_iter > 0) {
+      ptx::mbar_expect_tx(kv_full, 2 * C::TILE_BYTES);
+#pragma unroll
+      for (int blk = 0; blk < C::NBLK; ++blk) {
+        ptx::tma_load_4d(sK + blk * (BN * 128), &tmK, kv_full, blk * 64, kv0, h, b, ptx::kEvictFirst);
+        ptx::tma_load_4d(sV + blk * (BN * 128), &tmV, kv_full, blk * 64, kv0, h, b, ptx::kEvictFirst);
+      }
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int it = 0; it < n_iter; ++it) {
+        const int q0 = (i_start + it) * BM;
+        ptx::mbar_wait(&qdo_empty[stage], phase ^ 1);
+        ptx::mbar_expect_tx(&qdo_full[stage], 2 * C::TILE_BYTES);
+        uint8_t* dq_ = sStage + stage * 2 * C::TILE_BYTES;
+        uint8_t* ddo = dq_ + C::TILE_BYTES;
+#pragma unroll
+        for (int blk = 0; blk < C::NBLK; ++blk) {
+          ptx::tma_load_4d(dq_ + blk * (BM * 128), &tmQ, &qdo_full[stage], blk * 64, q0, h, b, ptx::kEvictLast);
+          ptx::tma_load_4d(ddo + blk * (BM * 128), &tmdO, &qdo_full[stage], blk * 64, q0, h, b, ptx::kEvictLast);
+        }
+        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 5) {
+    // ===================================== MMA issuer =====================================
+    if (ptx::elect_one() && n_iter > 0) {
+      constexpr uint32_t idesc_s = ptx::make_idesc(BM, BN, false, false);   // S, dP: both operands K-major
+      constexpr uint32_t idesc_dkv = ptx::make_idesc(BN, DP, true, true);   // dV, dK: A = Pᵀ/dSᵀ (MN), B MN
+      constexpr uint32_t idesc_dq = ptx::make_idesc(BM, DP, false, true);   // dQ: A = dS (K-major), B = K (MN)
+      const uint32_t k_addr = ptx::smem_u32(sK), v_addr = ptx::smem_u32(sV);
+      const uint32_t p_addr = ptx::smem_u32(sP), ds_addr = ptx::smem_u32(sdS);
+      const uint32_t st_addr = ptx::smem_u32(sStage);
+      ptx::mbar_wait(kv_full, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int it = 0; it < n_iter; ++it) {
+        const uint32_t q_addr = st_addr + stage * 2 * C::TILE_BYTES;
+        const uint32_t do_addr = q_addr + C::TILE_BYTES;
+        ptx::mbar_wait(&qdo_full[stage], phase);
+        if (C::ALIAS && it > 0) ptx::mbar_wait(dq_empty, (it - 1) & 1);
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < DP / 16; ++kk) {
+          const uint32_t off = (kk >> 2) * (128 * 128) + (kk & 3) * 32;
+          ptx::mma_f16_ss(tmem_base + C::COL_S, ptx::make_smem_desc(q_addr + off, 16, 1024),
+                          ptx::make_smem_desc(k_addr + off, 16, 1024), idesc_s, kk != 0);
+        }
+#pragma unroll
+        for (int kk = 0; kk < DP / 16; ++kk) {
+          const uint32_t off = (kk >> 2) * (128 * 128) + (kk & 3) * 32;
+          ptx::mma_f16_ss(tmem_base + C::COL_DP, ptx::make_smem_desc(do_addr + off, 16, 1024),
+                          ptx::make_smem_desc(v_addr + off, 16, 1024), idesc_s, kk != 0);
+        }
+        ptx::mma_commit(sdp_full);
+        ptx::mbar_wait(pds_full, it & 1);
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < BM / 16; ++kk) {  // reduction over the 128 query rows of the tile
+          // A: [q rows][keys] tile read MN-major (M = keys): 16 q-rows = 2048 B, 64-key blocks BM*128 B apart
+          // B: [q rows][D] tile read MN-major (N = D)
+          const uint32_t acc = (it > 0 || kk > 0) ? 1u : 0u;
+          ptx::mma_f16_ss(tmem_base + C::COL_DV, ptx::make_smem_desc(p_addr + kk * 2048, BM * 128, 1024),
+                          ptx::make_smem_desc(do_addr + kk * 2048, BM * 128, 1024), idesc_dkv, acc);
+        }
+#pragma unroll
+        for (int kk = 0; kk < BM / 16; ++kk) {
+          const uint32_t acc = (it > 0 || kk > 0) ? 1u : 0u;
+          ptx::mma_f16_ss(tmem_base + C::COL_DK, ptx::make_smem_desc(ds_addr + kk * 2048, BM * 128, 1024),
+                          ptx::make_smem_desc(q_addr + kk * 2048, BM * 128, 1024), idesc_dkv, acc);
+        }
+        if (!C::ALIAS && it > 0) {
+          ptx::mbar_wait(dq_empty, (it - 1) & 1);
+          ptx::tc_fence_after();
+        }
+#pragma unroll
+        for (int kk = 0; kk < BN / 16; ++kk) {  // reduction over the 128 keys
+          const uint32_t a_off = (kk >> 2) * (BM * 128) + (kk & 3) * 32;
+          ptx::mma_f16_ss(tmem_base + C::COL_DQ, ptx::make_smem_desc(ds_addr + a_off, 16, 1024),
+                          ptx::make_smem_desc(k_addr + kk * 2048, BN * 128, 1024), idesc_dq, kk != 0);
+        }
+        ptx::mma_commit(&qdo_empty[stage]);
+        ptx::mma_commit(dq_full);
+        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else {
+    // ===================================== softmax / dS warpgroup =====================================
+    const int r = warp * 32 + lane;
+    const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+    const long long bh = (long long)b * p.H + h;
+    for (int it = 0; it < n_iter; ++it) {
+      const int q0 = (i_start + it) * BM;
+      const int row = q0 + r;
+      const bool row_ok = row < p.Nq;
+      const float L2 = row_ok ? p.lse[bh * p.Nq + row] * kLog2e : INFINITY;
+      const float dl = row_ok ? p.delta[bh * p.Nq + row] : 0.f;
+      const bool need_mask = (kv0 + BN > p.Nk) || (p.causal && kv0 + BN - 1 > q0);
+      ptx::mbar_wait(sdp_full, it & 1);
+      ptx::tc_fence_after();
+#pragma unroll
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t s[32], dp[32];
+        ptx::tmem_ld_32x32b_x32(tmem_base + C::COL_S + lane_base + c * 32, s);
+        ptx::tmem_ld_32x32b_x32(tmem_base + C::COL_DP + lane_base + c * 32, dp);
+        ptx::tmem_ld_wait();
+        float pv[32], dsv[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float e = exp2f(fmaf(__uint_as_float(s[i]), p.scale_log2, -L2));
+          if (need_mask) {
+            const int col = kv0 + c * 32 + i;
+            const bool ok = col < p.Nk && (!p.causal || col <= row);
+            e = ok ? e : 0.f;
+          }
+          pv[i] = e;
+          dsv[i] = e * (__uint_as_float(dp[i]) - dl) * p.scale;
+        }
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          u32x4 o;
+          o.x = pack_bf16x2(pv[8 * v + 0], pv[8 * v + 1]);
+          o.y = pack_bf16x2(pv[8 * v + 2], pv[8 * v + 3]);
+          o.z = pack_bf16x2(pv[8 * v + 4], pv[8 * v + 5]);
+          o.w = pack_bf16x2(pv[8 * v + 6], pv[8 * v + 7]);
+          const uint32_t off = swz_off_b(r, c * 32 + v * 8, BM);
+          *reinterpret_cast<u32x4*>(sP + off) = o;
+          o.x = pack_bf16x2(dsv[8 * v + 0], dsv[8 * v + 1]);
+          o.y = pack_bf16x2(dsv[8 * v + 2], dsv[8 * v + 3]);
+          o.z = pack_bf16x2(dsv[8 * v + 4], dsv[8 * v + 5]);
+          o.w = pack_bf16x2(dsv[8 * v + 6], dsv[8 * v + 7]);
+          *reinterpret_cast<u32x4*>(sdS + off) = o;
+        }
+      }
+      ptx::tc_fence_before();
+      ptx::fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(pds_full);
+      // ---- drain the dQ partial of this (i, j) pair into the fp32 accumulator
+      ptx::mbar_wait(dq_full, it & 1);
+      ptx::tc_fence_after();
+      float* dq_row = p.dq_acc + (bh * p.Nq + row) * (long long)p.D;
+#pragma unroll
+      for (int c = 0; c < DP / 32; ++c) {
+        uint32_t t[32];
+        ptx::tmem_ld_32x32b_x32(tmem_base + C::COL_DQ + lane_base + c * 32, t);
+        ptx::tmem_ld_wait();
+        if (row_ok) {
+          if ((p.D & 3) == 0) {
+#pragma unroll
+            for (int v = 0; v < 8; ++v) {
+              const int col = c * 32 + v * 4;
+              if (col < p.D)
+                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dq_row + col),
+                             "f"(__uint_as_float(t[4 * v + 0])), "f"(__uint_as_float(t[4 * v + 1])),
+                             "f"(__uint_as_float(t[4 * v + 2])), "f"(__uint_as_float(t[4 * v + 3]))
+                             : "memory");
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (c * 32 + i < p.D) atomicAdd(dq_row + c * 32 + i, __uint_as_float(t[i]));
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(dq_empty);
+    }
+
+    // ---- epilogue: dK_j, dV_j (row r of the tile = key kv0 + r)
+    const int key = kv0 + r;
+    if (n_iter > 0) ptx::tc_fence_after();
+    __nv_bfloat16* dk_row = p.dk + (long long)b * p.dk_sb + (long long)h * p.dk_sh + (long long)key * p.dk_sr;
+    __nv_bfloat16* dv_row = p.dv + (long long)b * p.dv_sb + (long long)h * p.dv_sh + (long long)key * p.dv_sr;
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+      __nv_bfloat16* out = which == 0 ? dv_row : dk_row;
+      const uint32_t col0 = which == 0 ? C::COL_DV : C::COL_DK;
+      const bool vec = ((reinterpret_cast<uintptr_t>(out) & 15) == 0) && (p.D % 8 == 0);
+#pragma unroll
+      for (int c = 0; c < DP / 32; ++c) {
+        uint32_t t[32];
+        if (n_iter > 0) {
+          ptx::tmem_ld_32x32b_x32(tmem_base + col0 + lane_base + c * 32, t);
+          ptx::tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) t[i] = 0u;
+        }
+        if (key < p.Nk) {
+          if (vec) {
+#pragma unroll
+            for (int v = 0; v < 4; ++v) {
+              if (c * 32 + v * 8 < p.D) {
+                u32x4 o;
+                o.x = pack_bf16x2(__uint_as_float(t[8 * v + 0]), __uint_as_float(t[8 * v + 1]));
+                o.y = pack_bf16x2(__uint_as_float(t[8 * v + 2]), __uint_as_float(t[8 * v + 3]));
+                o.z = pack_bf16x2(__uint_as_float(t[8 * v + 4]), __uint_as_float(t[8 * v + 5]));
+                o.w = pack_bf16x2(__uint_as_float(t[8 * v + 6]), __uint_as_float(t[8 * v + 7]));
+                *reinterpret_cast<u32x4*>(out + c * 32 + v * 8) = o;
+              }
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (c * 32 + i < p.D) out[c * 32 + i] = __float2bfloat16(__uint_as_float(t[i]));
+          }
+        }
+      }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 5) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, C::TMEM_COLS);
+  }
+}
+
+// delta[b,h,i] = sum_d O[b,h,i,d] * dO[b,h,i,d]; one warp per row
+__global__ void fa2_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ dout,
+                                 float* __restrict__ delta, int H, int Nq, int D, long long o_sb, long long o_sh,
+                                 long long o_sr, long long d_sb, long long d_sh, long long d_sr, long long rows) {
+  const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (w >= rows) return;
+  const int i = (int)(w % Nq);
+  const long long bh = w / Nq;
+  const int hh = (int)(bh % H);
+  const long long bb = bh / H;
+  const __nv_bfloat16* orow = o + bb * o_sb + hh * o_sh + (long long)i * o_sr;
+  const __nv_bfloat16* drow = dout + bb * d_sb + hh * d_sh + (long long)i * d_sr;
+  float acc = 0.f;
+  for (int d = lane * 2; d < D; d += 64) {
+    const float2 a = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(orow + d));
+    const float2 g = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(drow + d));
+    acc += a.x * g.x + a.y * g.y;
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) delta[w] = acc;
+}
+
+__global__ void fa2_dq_convert_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dq, int H, int Nq,
+                                      int D, long long sb, long long sh, long long sr, long long total) {
+  const long long idx = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 2;
+  if (idx >= total) return;
+  const int d = (int)(idx % D);
+  const long long rowi = idx / D;
+  const int i = (int)(rowi % Nq);
+  const long long bh = rowi / Nq;
+  const int hh = (int)(bh % H);
+  const long long bb = bh / H;
+  const float2 v = *reinterpret_cast<const float2*>(acc + idx);
+  *reinterpret_cast<uint32_t*>(dq + bb * sb + hh * sh + (long long)i * sr + d) = pack_bf16x2(v.x, v.y);
+}
+
+template <int DP>
+static int launch_bwd(const CUtensorMap& q, const CUtensorMap& k, const CUtensorMap& v, const CUtensorMap& dO,
+                      const BwdParams& p, int B, cudaStream_t s) {
+  using C = BwdCfg<DP>;
+  auto kern = fa2_bwd_kernel<DP>;
+  static bool configured = false;
+  if (!configured) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+    configured = true;
+  }
+  dim3 grid(ceil_div(p.Nk, BN), p.H, B);
+  kern<<<grid, kThreads, C::SMEM_BYTES, s>>>(q, k, v, dO, p);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace fa2
+}  // namespace b200
+
+extern "C" int b200_fa2_bwd(const void* q, const void* k, const void* v, const void* o, const float* lse,
+                            const void* dout, void* dq, void* dk, void* dv, float* delta, float* dq_acc, int B, int H,
+                            int Nq, int Nk, int D, const long long* q_strides, const long long* k_strides,
+                            const long long* v_strides, const long long* o_strides, const long long* do_strides,
+                            const long long* dq_strides, const long long* dk_strides, const long long* dv_strides,
+                            int causal, float scale, void* stream) {
+  using namespace b200;
+  using namespace b200::fa2;
+  B200_REQUIRE(B > 0 && H > 0 && Nq > 0 && Nk > 0, "fa2_bwd: empty problem");
+  B200_REQUIRE(D >= 8 && D <= 128 && D % 8 == 0, "fa2_bwd: head dim %d unsupported (multiple of 8, <= 128)", D);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const long long rows = (long long)B * H * Nq;
+  {
+    const int threads = 256;
+    const long long blocks = (rows * 32 + threads - 1) / threads;
+    fa2_delta_kernel<<<(unsigned)blocks, threads, 0, s>>>(
+        reinterpret_cast<const __nv_bfloat16*>(o), reinterpret_cast<const __nv_bfloat16*>(dout), delta, H, Nq, D,
+        o_strides[0], o_strides[1], o_strides[2], do_strides[0], do_strides[1], do_strides[2], rows);
+    B200_LAUNCH_CHECK();
+  }
+  B200_CHECK_CUDA(cudaMemsetAsync(dq_acc, 0, (size_t)rows * D * sizeof(float), s));
+  CUtensorMap tq, tk, tv, tdo;
+  int rc;
+  if ((rc = make_bhnd_map(&tq, q, B, H, Nq, D, q_strides, BM))) return rc;
+  if ((rc = make_bhnd_map(&tk, k, B, H, Nk, D, k_strides, BN))) return rc;
+  if ((rc = make_bhnd_map(&tv, v, B, H, Nk, D, v_strides, BN))) return rc;
+  if ((rc = make_bhnd_map(&tdo, dout, B, H, Nq, D, do_strides, BM))) return rc;
+  BwdParams p;
+  p.lse = lse; p.delta = delta; p.dq_acc = dq_acc;
+  p.dk = reinterpret_cast<__nv_bfloat16*>(dk); p.dv = reinterpret_cast<__nv_bfloat16*>(dv);
+  p.dk_sb = dk_strides[0]; p.dk_sh = dk_strides[1]; p.dk_sr = dk_strides[2];
+  p.dv_sb = dv_strides[0]; p.dv_sh = dv_strides[1]; p.dv_sr = dv_strides[2];
+  p.H = H; p.Nq = Nq; p.Nk = Nk; p.D = D; p.causal = causal;
+  p.scale = scale; p.scale_log2 = scale * kLog2e;
+  p.num_q_tiles = ceil_div(Nq, BM);
+  rc = D <= 64 ? launch_bwd<64>(tq, tk, tv, tdo, p, B, s) : launch_bwd<128>(tq, tk, tv, tdo, p, B, s);
+  if (rc) return rc;
+  {
+    const long long total = rows * D;
+    const int threads = 256;
+    fa2_dq_convert_kernel<<<(unsigned)((total / 2 + threads - 1) / threads), threads, 0, s>>>(
+        dq_acc, reinterpret_cast<__nv_bfloat16*>(dq), H, Nq, D, dq_strides[0], dq_strides[1], dq_strides[2], total);
+    B200_LAUNCH_CHECK();
+  }
+  return 0;
+}

@@ -1,0 +1,379 @@
+// Persistent warp-specialised bf16 GEMM on tcgen05 / TMEM / TMA for sm_100a.
+//
+//   C[M,N] = A · Bᵀ   with fp32 accumulation in tensor memory,
+//   A given K-major ([M,K] row-major) or MN-major ([K,M] row-major),
+//   B given K-major ([N,K] row-major) or MN-major ([K,N] row-major),
+// which covers the three GEMMs of a linear layer without any transposed copy:
+//   forward  y  = x·Wᵀ      A = x  (K-major)   B = W  (K-major)
+//   dgrad    dx = dy·W      A = dy (K-major)   B = W  (MN-major)
+//   wgrad    dW = dyᵀ·x     A = dy (MN-major)  B = x  (MN-major)
+// Replaces the cuBLAS calls behind every `Linear` of the reference LM
+// (cs336-basics/cs336_basics/model.py:41).
+//
+// Structure (one CTA per SM, 256 threads):
+//   warp 0   TMA producer    — cp.async.bulk.tensor loads of 128×64 A and BN×64 B tiles (128B swizzle)
+//                              into a STAGES-deep shared-memory ring, mbarrier complete_tx
+//   warp 1   MMA issuer      — one elected thread issues tcgen05.mma (M=128, N=BN, K=16) ×4 per stage,
+//                              tcgen05.commit frees the stage / publishes the accumulator
+//   warp 2   TMEM allocator  — 512 columns = two BN-wide fp32 accumulators (double buffered)
+//   warps 4-7 epilogue       — tcgen05.ld 32 lanes × 32 columns, convert, vectorised global stores;
+//                              overlaps the next tile's main loop through the second accumulator
+#include "common.cuh"
+#include "ptx.cuh"
+#include "tensormap.h"
+
+namespace b200 {
+namespace gemm {
+
+constexpr int BM = 128;
+constexpr int BK = 64;  // 64 bf16 = one 128-byte swizzle row
+constexpr int kThreads = 256;
+constexpr int kTmemCols = 512;
+
+enum Epilogue : int {
+  EPI_BF16 = 0,      // C bf16 = acc
+  EPI_F32 = 1,       // C fp32 = acc
+  EPI_F32_ACC = 2,   // C fp32 += acc
+  EPI_BF16_SWIGLU = 3,  // C bf16 [M, N/2] = silu(acc[:, 2j]) * acc[:, 2j+1]   (interleaved gate/up columns)
+  EPI_F32_RESID = 4,    // C fp32 = aux fp32 + acc   (residual add)
+};
+
+struct Params {
+  void* C;
+  const void* aux;
+  int M, N, K;
+  int ldc, ld_aux;
+  int num_m, num_n, num_k;
+};
+
+template <int BN>
+struct Cfg {
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int MAX_STAGES = (227 * 1024 - 2048) / STAGE_BYTES;
+  static constexpr int STAGES = MAX_STAGES > 8 ? 8 : MAX_STAGES;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 512 /*barriers*/;
+};
+
+template <int EPI>
+__device__ __forceinline__ void store_chunk(const Params& p, int row, int col0, const uint32_t (&r)[32]) {
+  // one thread owns one output row; r[] holds 32 consecutive fp32 accumulator columns
+  if (row >= p.M || col0 >= p.N) return;
+  const bool full = (col0 + 32 <= p.N);
+  if constexpr (EPI == EPI_BF16) {
+    __nv_bfloat16* c = reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + col0;
+    if (full && (p.ldc & 7) == 0) {
+#pragma unroll
+      for (int v = 0; v < 4; ++v) {
+        u32x4 o;
+        o.x = pack_bf16x2(__uint_as_float(r[8 * v + 0]), __uint_as_float(r[8 * v + 1]));
+        o.y = pack_bf16x2(__uint_as_float(r[8 * v + 2]), __uint_as_float(r[8 * v + 3]));
+        o.z = pack_bf16x2(__uint_as_float(r[8 * v + 4]), __uint_as_float(r[8 * v + 5]));
+        o.w = pack_bf16x2(__uint_as_float(r[8 * v + 6]), __uint_as_float(r[8 * v + 7]));
+        *reinterpret_cast<u32x4*>(c + 8 * v) = o;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j < p.N) c[j] = __float2bfloat16(__uint_as_float(r[j]));
+    }
+  } else if constexpr (EPI == EPI_F32 || EPI == EPI_F32_ACC || EPI == EPI_F32_RESID) {
+    float* c = reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0;
+    const float* x = nullptr;
+    if constexpr (EPI == EPI_F32_ACC) x = c;
+    if constexpr (EPI == EPI_F32_RESID) x = reinterpret_cast<const float*>(p.aux) + (size_t)row * p.ld_aux + col0;
+    const bool vec = full && (p.ldc & 3) == 0 && (EPI != EPI_F32_RESID || (p.ld_aux & 3) == 0);
+    if (vec) {
+#pragma unroll
+      for (int v = 0; v < 8; ++v) {
+        f32x4 o;
+        o.x = __uint_as_float(r[4 * v + 0]);
+        o.y = __uint_as_float(r[4 * v + 1]);
+        o.z = __uint_as_float(r[4 * v + 2]);
+        o.w = __uint_as_float(r[4 * v + 3]);
+        if constexpr (EPI != EPI_F32) {
+          f32x4 old = *reinterpret_cast<const f32x4*>(x + 4 * v);
+          o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+        }
+        *reinterpret_cast<f32x4*>(c + 4 * v) = o;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j < p.N) {
+          float v = __uint_as_float(r[j]);
+          if constexpr (EPI != EPI_F32) v += x[j];
+          c[j] = v;
+        }
+    }
+  } else if constexpr (EPI == EPI_BF16_SWIGLU) {
+    // columns (2j, 2j+1) = (gate, up) of hidden unit (col0/2 + j); output has N/2 columns
+    __nv_bfloat16* c = reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + (col0 >> 1);
+    float g[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const float a = __uint_as_float(r[2 * j]), b = __uint_as_float(r[2 * j + 1]);
+      g[j] = a / (1.f + __expf(-a)) * b;
+    }
+    if (full && (p.ldc & 7) == 0) {
+#pragma unroll
+      for (int v = 0; v < 2; ++v) {
+        u32x4 o;
+        o.x = pack_bf16x2(g[8 * v + 0], g[8 * v + 1]);
+        o.y = pack_bf16x2(g[8 * v + 2], g[8 * v + 3]);
+        o.z = pack_bf16x2(g[8 * v + 4], g[8 * v + 5]);
+        o.w = pack_bf16x2(g[8 * v + 6], g[8 * v + 7]);
+        *reinterpret_cast<u32x4*>(c + 8 * v) = o;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 16; ++j)
+        if (col0 + 2 * j + 1 < p.N) c[j] = __float2bfloat16(g[j]);
+    }
+  }
+}
+
+template <int BN, bool A_MN, bool B_MN, int EPI>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params p) {
+  using C = Cfg<BN>;
+  constexpr int STAGES = C::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * C::STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && ptx::elect_one()) {
+    ptx::tma_prefetch_desc(&tmA);
+    ptx::tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && ptx::elect_one()) {
+    for (int s = 0; s < STAGES; ++s) {
+      ptx::mbar_init(&full_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      ptx::mbar_init(&tfull_bar[a], 1);
+      ptx::mbar_init(&tempty_bar[a], 4);  // one arrive per epilogue warp
+    }
+    ptx::fence_mbar_init();
+  }
+  if (warp == 2) {
+    ptx::tmem_alloc(tmem_slot, kTmemCols);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int total_tiles = p.num_m * p.num_n;
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (ptx::elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int m0 = (t % p.num_m) * BM;
+        const int n0 = (t / p.num_m) * BN;
+        for (int kb = 0; kb < p.num_k; ++kb) {
+          ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+          ptx::mbar_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+          uint8_t* sa = smem + stage * C::STAGE_BYTES;
+          uint8_t* sb = sa + C::A_BYTES;
+          if constexpr (!A_MN) {
+            ptx::tma_load_2d(sa, &tmA, &full_bar[stage], kb * BK, m0);
+          } else {
+#pragma unroll
+            for (int c = 0; c < BM / 64; ++c)
+              ptx::tma_load_2d(sa + c * (64 * BK * 2), &tmA, &full_bar[stage], m0 + c * 64, kb * BK);
+          }
+          if constexpr (!B_MN) {
+            ptx::tma_load_2d(sb, &tmB, &full_bar[stage], kb * BK, n0);
+          } else {
+#pragma unroll
+            for (int c = 0; c < BN / 64; ++c)
+              ptx::tma_load_2d(sb + c * (64 * BK * 2), &tmB, &full_bar[stage], n0 + c * 64, kb * BK);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer ================================
+    if (ptx::elect_one()) {
+      constexpr uint32_t idesc = ptx::make_idesc(BM, BN, A_MN, B_MN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        ptx::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < p.num_k; ++kb) {
+          ptx::mbar_wait(&full_bar[stage], phase);
+          ptx::tc_fence_after();
+          const uint32_t a_addr = ptx::smem_u32(smem + stage * C::STAGE_BYTES);
+          const uint32_t b_addr = a_addr + C::A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            // K-major: advance 16 elements = 32 B inside the swizzled row; MN-major: 16 K-rows = 2048 B
+            const uint64_t adesc = A_MN ? ptx::make_smem_desc(a_addr + k * 2048, 64 * BK * 2, 1024)
+                                        : ptx::make_smem_desc(a_addr + k * 32, 16, 1024);
+            const uint64_t bdesc = B_MN ? ptx::make_smem_desc(b_addr + k * 2048, 64 * BK * 2, 1024)
+                                        : ptx::make_smem_desc(b_addr + k * 32, 16, 1024);
+            ptx::mma_f16_ss(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          ptx::mma_commit(&empty_bar[stage]);  // stage reusable once these MMAs have read it
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        ptx::mma_commit(&tfull_bar[acc]);  // accumulator complete
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ================================ epilogue ================================
+    const int ew = warp - 4;  // == warp % 4: TMEM lane quadrant this warp may access
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      const int m0 = (t % p.num_m) * BM;
+      const int n0 = (t / p.num_m) * BN;
+      ptx::mbar_wait(&tfull_bar[acc], acc_phase);
+      ptx::tc_fence_after();
+      const int row = m0 + ew * 32 + lane;
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        if (n0 + c * 32 >= p.N) break;  // warp-uniform
+        uint32_t r[32];
+        ptx::tmem_ld_32x32b_x32(t_row + c * 32, r);
+        ptx::tmem_ld_wait();
+        store_chunk<EPI>(p, row, n0 + c * 32, r);
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&tempty_bar[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+static int pick_bn(int M, int N, bool need64) {
+  // minimise (waves × tile width); wider tiles get a small bonus (less smem traffic per MMA)
+  const int cands[3] = {256, 192, 128};
+  const double penalty[3] = {1.0, 1.04, 1.12};
+  int best = 256;
+  double best_cost = 1e30;
+  const int nm = ceil_div(M, BM);
+  for (int i = 0; i < 3; ++i) {
+    const int bn = cands[i];
+    (void)need64;
+    const int tiles = nm * ceil_div(N, bn);
+    const int waves = ceil_div(tiles, num_sms());
+    const double cost = (double)waves * bn * penalty[i];
+    if (cost < best_cost) { best_cost = cost; best = bn; }
+  }
+  return best;
+}
+
+template <int BN, bool A_MN, bool B_MN, int EPI>
+static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Params& p, cudaStream_t stream) {
+  using C = Cfg<BN>;
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, EPI>;
+  static bool configured = false;  // per instantiation
+  if (!configured) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+    configured = true;
+  }
+  const int tiles = p.num_m * p.num_n;
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  kern<<<grid, kThreads, C::SMEM_BYTES, stream>>>(tmA, tmB, p);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static int dispatch_epi(int epi, const CUtensorMap& a, const CUtensorMap& b, const Params& p, cudaStream_t s) {
+  switch (epi) {
+    case EPI_BF16: return launch<BN, A_MN, B_MN, EPI_BF16>(a, b, p, s);
+    case EPI_F32: return launch<BN, A_MN, B_MN, EPI_F32>(a, b, p, s);
+    case EPI_F32_ACC: return launch<BN, A_MN, B_MN, EPI_F32_ACC>(a, b, p, s);
+    case EPI_BF16_SWIGLU:
+      if constexpr (!A_MN && !B_MN) return launch<BN, A_MN, B_MN, EPI_BF16_SWIGLU>(a, b, p, s);
+      break;
+    case EPI_F32_RESID:
+      if constexpr (!A_MN && !B_MN) return launch<BN, A_MN, B_MN, EPI_F32_RESID>(a, b, p, s);
+      break;
+  }
+  set_error("gemm: unsupported epilogue %d for this operand layout", epi);
+  return B200_ERR_ARG;
+}
+
+template <int BN>
+static int dispatch_major(bool a_mn, bool b_mn, int epi, const CUtensorMap& a, const CUtensorMap& b, const Params& p,
+                          cudaStream_t s) {
+  if (!a_mn && !b_mn) return dispatch_epi<BN, false, false>(epi, a, b, p, s);
+  if (!a_mn && b_mn) return dispatch_epi<BN, false, true>(epi, a, b, p, s);
+  if (a_mn && b_mn) return dispatch_epi<BN, true, true>(epi, a, b, p, s);
+  return dispatch_epi<BN, true, false>(epi, a, b, p, s);
+}
+
+}  // namespace gemm
+}  // namespace b200
+
+extern "C" int b200_gemm_bf16(const void* A, const void* B, void* C, const void* aux, int M, int N, int K, int lda,
+                              int ldb, int ldc, int ld_aux, int a_mn_major, int b_mn_major, int epilogue,
+                              int force_bn, void* stream) {
+  using namespace b200;
+  using namespace b200::gemm;
+  B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
+  B200_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0, "gemm: lda/ldb must be multiples of 8 elements (TMA 16-byte strides)");
+  const bool a_mn = a_mn_major != 0, b_mn = b_mn_major != 0;
+  int bn = force_bn > 0 ? force_bn : pick_bn(M, N, a_mn || b_mn);
+  B200_REQUIRE(bn == 128 || bn == 192 || bn == 256, "gemm: BN must be 128, 192 or 256");
+
+  CUtensorMap tmA, tmB;
+  {
+    uint64_t dims[2], strides[1];
+    uint32_t box[2];
+    if (!a_mn) { dims[0] = (uint64_t)K; dims[1] = (uint64_t)M; box[0] = BK; box[1] = BM; }
+    else       { dims[0] = (uint64_t)M; dims[1] = (uint64_t)K; box[0] = 64; box[1] = BK; }
+    strides[0] = (uint64_t)lda * 2;
+    int rc = encode_tensor_map(&tmA, TmDtype::BF16, 2, A, dims, strides, box);
+    if (rc) return rc;
+    if (!b_mn) { dims[0] = (uint64_t)K; dims[1] = (uint64_t)N; box[0] = BK; box[1] = (uint32_t)bn; }
+    else       { dims[0] = (uint64_t)N; dims[1] = (uint64_t)K; box[0] = 64; box[1] = BK; }
+    strides[0] = (uint64_t)ldb * 2;
+    rc = encode_tensor_map(&tmB, TmDtype::BF16, 2, B, dims, strides, box);
+    if (rc) return rc;
+  }
+  Params p;
+  p.C = C; p.aux = aux; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.ld_aux = ld_aux;
+  p.num_m = ceil_div(M, BM); p.num_n = ceil_div(N, bn); p.num_k = ceil_div(K, BK);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  switch (bn) {
+    case 256: return dispatch_major<256>(a_mn, b_mn, epilogue, tmA, tmB, p, s);
+    case 192: return dispatch_major<192>(a_mn, b_mn, epilogue, tmA, tmB, p, s);
+    default: return dispatch_major<128>(a_mn, b_mn, epilogue, tmA, tmB, p, s);
+  }
+}

@@ -1,0 +1,218 @@
+// Fused RMSNorm (+ residual add) forward and backward.
+//
+// Replaces the ≈7 ATen kernels per RMSNorm call of the reference LM (model.py:101-107) and the
+// separate residual adds (model.py:380-386): one pass reads the fp32 residual stream (+ the bf16
+// branch output that still has to be added), writes the updated fp32 stream, the normalised bf16
+// activations for the next GEMM and the per-row rstd.  fp32 math throughout.
+#include "common.cuh"
+
+namespace b200 {
+
+template <typename T> __device__ __forceinline__ float ld_as_float(const T* p, size_t i);
+template <> __device__ __forceinline__ float ld_as_float<float>(const float* p, size_t i) { return p[i]; }
+template <> __device__ __forceinline__ float ld_as_float<__nv_bfloat16>(const __nv_bfloat16* p, size_t i) {
+  return __bfloat162float(p[i]);
+}
+template <typename T> __device__ __forceinline__ void st_from_float(T* p, size_t i, float v);
+template <> __device__ __forceinline__ void st_from_float<float>(float* p, size_t i, float v) { p[i] = v; }
+template <> __device__ __forceinline__ void st_from_float<__nv_bfloat16>(__nv_bfloat16* p, size_t i, float v) {
+  p[i] = __float2bfloat16(v);
+}
+
+// ---- forward ---------------------------------------------------------------------------------
+// one CTA per row; the row (after the optional residual add) is staged in shared memory as fp32
+template <typename TX, typename TY>
+__global__ void __launch_bounds__(256) rmsnorm_fwd_kernel(const TX* __restrict__ x, const __nv_bfloat16* __restrict__ resid,
+                                                          const float* __restrict__ w, TY* __restrict__ y,
+                                                          float* __restrict__ xout, float* __restrict__ rstd_out,
+                                                          int d, float eps) {
+  extern __shared__ float row[];
+  __shared__ float red[32];
+  const size_t base = (size_t)blockIdx.x * d;
+  float ss = 0.f;
+  if (sizeof(TX) == 4 && (d & 3) == 0) {
+    const f32x4* x4 = reinterpret_cast<const f32x4*>(reinterpret_cast<const float*>(x) + base);
+    for (int i = threadIdx.x; i < d / 4; i += blockDim.x) {
+      f32x4 v = x4[i];
+      if (resid) {
+        const uint2 rb = *reinterpret_cast<const uint2*>(resid + base + 4 * i);
+        const float2 r0 = unpack_bf16x2(rb.x), r1 = unpack_bf16x2(rb.y);
+        v.x += r0.x; v.y += r0.y; v.z += r1.x; v.w += r1.y;
+      }
+      if (xout) *reinterpret_cast<f32x4*>(xout + base + 4 * i) = v;
+      *reinterpret_cast<f32x4*>(row + 4 * i) = v;
+      ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    }
+  } else {
+    for (int i = threadIdx.x; i < d; i += blockDim.x) {
+      float v = ld_as_float<TX>(x, base + i);
+      if (resid) v += __bfloat162float(resid[base + i]);
+      if (xout) xout[base + i] = v;
+      row[i] = v;
+      ss += v * v;
+    }
+  }
+  ss = block_sum(ss, red);
+  const float rstd = rsqrtf(ss / (float)d + eps);
+  if (threadIdx.x == 0 && rstd_out) rstd_out[blockIdx.x] = rstd;
+  if (sizeof(TY) == 2 && (d & 7) == 0) {
+    for (int i = threadIdx.x; i < d / 8; i += blockDim.x) {
+      const f32x4 a = *reinterpret_cast<const f32x4*>(row + 8 * i), b = *reinterpret_cast<const f32x4*>(row + 8 * i + 4);
+      const f32x4 wa = *reinterpret_cast<const f32x4*>(w + 8 * i), wb = *reinterpret_cast<const f32x4*>(w + 8 * i + 4);
+      u32x4 o;
+      o.x = pack_bf16x2(a.x * rstd * wa.x, a.y * rstd * wa.y);
+      o.y = pack_bf16x2(a.z * rstd * wa.z, a.w * rstd * wa.w);
+      o.z = pack_bf16x2(b.x * rstd * wb.x, b.y * rstd * wb.y);
+      o.w = pack_bf16x2(b.z * rstd * wb.z, b.w * rstd * wb.w);
+      *reinterpret_cast<u32x4*>(reinterpret_cast<__nv_bfloat16*>(y) + base + 8 * i) = o;
+    }
+  } else {
+    for (int i = threadIdx.x; i < d; i += blockDim.x) st_from_float<TY>(y, base + i, row[i] * rstd * w[i]);
+  }
+}
+
+// ---- backward --------------------------------------------------------------------------------
+// dx = dres_in + rstd * (g - xhat * mean(g * xhat)),  g = dy * w,  xhat = x * rstd
+// dw[j] = sum_rows dy[r,j] * xhat[r,j]   (per-CTA partials in `dw_partial`, reduced by a 2nd kernel)
+template <typename TDY, int VPT>
+__global__ void __launch_bounds__(256) rmsnorm_bwd_kernel(const TDY* __restrict__ dy, const float* __restrict__ x,
+                                                          const float* __restrict__ w, const float* __restrict__ rstd,
+                                                          const float* __restrict__ dres_in, float* __restrict__ dx,
+                                                          __nv_bfloat16* __restrict__ dx_bf16,
+                                                          float* __restrict__ dw_partial, int T, int d) {
+  __shared__ float red[32];
+  float dw_acc[VPT];
+#pragma unroll
+  for (int v = 0; v < VPT; ++v) dw_acc[v] = 0.f;
+  for (int r = blockIdx.x; r < T; r += gridDim.x) {
+    const size_t base = (size_t)r * d;
+    const float rs = rstd[r];
+    float gx[VPT], xh[VPT];
+    float dot = 0.f;
+#pragma unroll
+    for (int v = 0; v < VPT; ++v) {
+      const int j = threadIdx.x + v * blockDim.x;
+      gx[v] = 0.f; xh[v] = 0.f;
+      if (j < d) {
+        const float dyv = ld_as_float<TDY>(dy, base + j);
+        xh[v] = x[base + j] * rs;
+        gx[v] = dyv * w[j];
+        dw_acc[v] += dyv * xh[v];
+        dot += gx[v] * xh[v];
+      }
+    }
+    dot = block_sum(dot, red) / (float)d;
+#pragma unroll
+    for (int v = 0; v < VPT; ++v) {
+      const int j = threadIdx.x + v * blockDim.x;
+      if (j < d) {
+        float o = rs * (gx[v] - xh[v] * dot);
+        if (dres_in) o += dres_in[base + j];
+        if (dx) dx[base + j] = o;
+        if (dx_bf16) dx_bf16[base + j] = __float2bfloat16(o);
+      }
+    }
+  }
+#pragma unroll
+  for (int v = 0; v < VPT; ++v) {
+    const int j = threadIdx.x + v * blockDim.x;
+    if (j < d) dw_partial[(size_t)blockIdx.x * d + j] = dw_acc[v];
+  }
+}
+
+__global__ void colsum_kernel(const float* __restrict__ partial, float* __restrict__ out, int rows, int d,
+                              int accumulate) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= d) return;
+  float s = 0.f;
+  for (int r = 0; r < rows; ++r) s += partial[(size_t)r * d + j];
+  out[j] = accumulate ? out[j] + s : s;
+}
+
+// residual add: out fp32 = x fp32 + y bf16
+__global__ void residual_add_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ y,
+                                    float* __restrict__ out, size_t n) {
+  const size_t i4 = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i4 + 3 < n) {
+    f32x4 v = *reinterpret_cast<const f32x4*>(x + i4);
+    const uint2 rb = *reinterpret_cast<const uint2*>(y + i4);
+    const float2 a = unpack_bf16x2(rb.x), b = unpack_bf16x2(rb.y);
+    v.x += a.x; v.y += a.y; v.z += b.x; v.w += b.y;
+    *reinterpret_cast<f32x4*>(out + i4) = v;
+  } else {
+    for (size_t i = i4; i < n; ++i) out[i] = x[i] + __bfloat162float(y[i]);
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_rmsnorm_fwd(const void* x, int x_dtype, const void* resid_bf16, const float* w, void* y,
+                                int y_dtype, float* xout, float* rstd, int T, int d, float eps, void* stream) {
+  B200_REQUIRE(T > 0 && d > 0, "rmsnorm_fwd: empty input");
+  B200_REQUIRE(d * 4 <= 160 * 1024, "rmsnorm_fwd: hidden size %d too large for the smem-staged kernel", d);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int threads = d >= 2048 ? 256 : 128;
+  const size_t smem = (size_t)d * 4;
+#define LAUNCH(TX, TY)                                                                                            \
+  do {                                                                                                            \
+    auto k = rmsnorm_fwd_kernel<TX, TY>;                                                                          \
+    if (smem > 48 * 1024) B200_CHECK_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    k<<<T, threads, smem, s>>>(reinterpret_cast<const TX*>(x), reinterpret_cast<const __nv_bfloat16*>(resid_bf16), w, \
+                               reinterpret_cast<TY*>(y), xout, rstd, d, eps);                                     \
+  } while (0)
+  if (x_dtype == B200_F32 && y_dtype == B200_BF16) LAUNCH(float, __nv_bfloat16);
+  else if (x_dtype == B200_F32 && y_dtype == B200_F32) LAUNCH(float, float);
+  else if (x_dtype == B200_BF16 && y_dtype == B200_BF16) LAUNCH(__nv_bfloat16, __nv_bfloat16);
+  else if (x_dtype == B200_BF16 && y_dtype == B200_F32) LAUNCH(__nv_bfloat16, float);
+  else { set_error("rmsnorm_fwd: bad dtypes %d -> %d", x_dtype, y_dtype); return B200_ERR_ARG; }
+#undef LAUNCH
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200_rmsnorm_bwd_workspace_rows(int T) {
+  const int cap = num_sms() * 2;
+  return T < cap ? T : cap;
+}
+
+// scratch: b200_rmsnorm_bwd_workspace_rows(T) * d floats
+extern "C" int b200_rmsnorm_bwd(const void* dy, int dy_dtype, const float* x, const float* w, const float* rstd,
+                                const float* dres_in, float* dx, void* dx_bf16, float* dw, int dw_accumulate,
+                                float* scratch, int T, int d, void* stream) {
+  B200_REQUIRE(T > 0 && d > 0, "rmsnorm_bwd: empty input");
+  B200_REQUIRE(d <= 256 * 48, "rmsnorm_bwd: hidden size %d too large", d);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int grid = b200_rmsnorm_bwd_workspace_rows(T);
+  __nv_bfloat16* dxb = reinterpret_cast<__nv_bfloat16*>(dx_bf16);
+#define LAUNCH(TDY, VPT, THREADS)                                                                              \
+  rmsnorm_bwd_kernel<TDY, VPT><<<grid, THREADS, 0, s>>>(reinterpret_cast<const TDY*>(dy), x, w, rstd, dres_in, dx, \
+                                                        dxb, scratch, T, d)
+#define BY_DTYPE(VPT, THREADS)                                              \
+  do {                                                                      \
+    if (dy_dtype == B200_BF16) LAUNCH(__nv_bfloat16, VPT, THREADS);         \
+    else LAUNCH(float, VPT, THREADS);                                       \
+  } while (0)
+  if (d <= 128 * 4) BY_DTYPE(4, 128);
+  else if (d <= 128 * 8) BY_DTYPE(8, 128);
+  else if (d <= 256 * 8) BY_DTYPE(8, 256);
+  else if (d <= 256 * 16) BY_DTYPE(16, 256);
+  else BY_DTYPE(48, 256);
+#undef BY_DTYPE
+#undef LAUNCH
+  B200_LAUNCH_CHECK();
+  colsum_kernel<<<ceil_div(d, 128), 128, 0, s>>>(scratch, dw, grid, d, dw_accumulate);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200_residual_add(const float* x, const void* y_bf16, float* out, long long n, void* stream) {
+  if (n <= 0) return 0;
+  const int threads = 256;
+  const long long nvec = (n + 3) / 4;
+  residual_add_kernel<<<(unsigned)((nvec + threads - 1) / threads), threads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      x, reinterpret_cast<const __nv_bfloat16*>(y_bf16), out, (size_t)n);
+  B200_LAUNCH_CHECK();
+  return 0;
+}

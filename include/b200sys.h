@@ -1,0 +1,125 @@
+/* libb200sys — C ABI of the hand-written sm_100a (B200) kernels.
+ *
+ * Conventions
+ *  - every entry point returns 0 on success; on failure a non-zero code and a message retrievable
+ *    with b200_last_error() (thread-local);
+ *  - pointers are device pointers unless the name ends in _host; `stream` is a cudaStream_t;
+ *  - nothing here synchronises the host with the device;
+ *  - "ref:" comments name the code of the reference (kkaitlyn111/cs336-a2-systems) whose work the
+ *    kernel replaces.
+ */
+#ifndef B200SYS_H_
+#define B200SYS_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { B200_OK = 0, B200_ERR_ARG = 1, B200_ERR_CUDA = 2, B200_ERR_UNSUPPORTED = 3 };
+enum { B200_BF16 = 0, B200_F32 = 1 };
+
+const char* b200_last_error(void);
+int b200_version(void);
+int b200_device_info(int* sm_count, int* cc_major, int* cc_minor);
+
+/* ---- tcgen05 GEMM --------------------------------------------------------------------------
+ * C[M,N] = A · Bᵀ, bf16 operands, fp32 accumulation in tensor memory.
+ *   a_mn_major = 0: A stored [M,K] row-major (lda = row stride);  1: A stored [K,M] row-major.
+ *   b_mn_major = 0: B stored [N,K] row-major (ldb = row stride);  1: B stored [K,N] row-major.
+ *   epilogue: 0 C bf16 = acc | 1 C fp32 = acc | 2 C fp32 += acc |
+ *             3 C bf16 [M,N/2] = silu(acc[:,2j])*acc[:,2j+1] | 4 C fp32 = aux fp32 + acc
+ *   force_bn: 0 = heuristic, else tile width 128/192/256.
+ * ref: every Linear of the LM → cuBLAS (cs336-basics/cs336_basics/model.py:41). */
+int b200_gemm_bf16(const void* A, const void* B, void* C, const void* aux, int M, int N, int K, int lda, int ldb,
+                   int ldc, int ld_aux, int a_mn_major, int b_mn_major, int epilogue, int force_bn, void* stream);
+
+/* ---- FlashAttention-2 (tcgen05/TMEM/TMA) ------------------------------------------------------
+ * q,k,v,o: bf16 with element strides (batch, head, row); last dim contiguous, D in {16,32,64,80,96,128}.
+ * lse: fp32 [B,H,Nq] contiguous.  scale = 1/sqrt(D) is applied inside.
+ * ref: Triton flash_attention_kernel (cs336_systems/flash_attention.py:137-266). */
+int b200_fa2_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int H, int Nq, int Nk,
+                 int D, const long long* q_strides, const long long* k_strides, const long long* v_strides,
+                 const long long* o_strides, int causal, float scale, void* stream);
+/* delta: fp32 [B,H,Nq] scratch (rowsum(O∘dO)); dq_acc: fp32 [B,H,Nq,D] scratch, zeroed inside.
+ * dq,dk,dv: bf16 with their own strides.
+ * ref: torch.compile'd backward_pass_recomp materialising N×N matrices (flash_attention.py:270-289). */
+int b200_fa2_bwd(const void* q, const void* k, const void* v, const void* o, const float* lse, const void* dout,
+                 void* dq, void* dk, void* dv, float* delta, float* dq_acc, int B, int H, int Nq, int Nk, int D,
+                 const long long* q_strides, const long long* k_strides, const long long* v_strides,
+                 const long long* o_strides, const long long* do_strides, const long long* dq_strides,
+                 const long long* dk_strides, const long long* dv_strides, int causal, float scale, void* stream);
+
+/* ---- fused normalisation / elementwise ---------------------------------------------------------
+ * ref: RMSNorm model.py:101-107, residual adds model.py:380-386. */
+int b200_rmsnorm_fwd(const void* x, int x_dtype, const void* resid_bf16 /*nullable*/, const float* w, void* y,
+                     int y_dtype, float* xout /*nullable: x+resid in fp32*/, float* rstd /*nullable*/, int T, int d,
+                     float eps, void* stream);
+int b200_rmsnorm_bwd_workspace_rows(int T);
+int b200_rmsnorm_bwd(const void* dy, int dy_dtype, const float* x, const float* w, const float* rstd,
+                     const float* dres_in /*nullable*/, float* dx /*nullable*/, void* dx_bf16 /*nullable*/, float* dw,
+                     int dw_accumulate, float* scratch /* workspace_rows(T)*d floats */, int T, int d, void* stream);
+int b200_residual_add(const float* x, const void* y_bf16, float* out, long long n, void* stream);
+/* ref: RoPE model.py:135-147 (interleaved pairs); qkv is [B,S,3,H,dh] bf16, q and k rotated in place. */
+int b200_rope_qk_inplace(void* qkv_bf16, const float* cache /*(2,ctx,dh/2)*/, int ctx, int B, int S, int H, int dh,
+                         int inverse, void* stream);
+/* ref: silu(w1 x) * w3 x, model.py:397,526-527.  ab = [T, 2F] (gate | up). */
+int b200_swiglu_fwd(const void* ab, void* g, long long T, int F, void* stream);
+int b200_swiglu_bwd(const void* ab, const void* dg, void* dab, long long T, int F, void* stream);
+/* ref: Embedding gather model.py:57 and its scatter-add backward. */
+int b200_embedding_fwd(const long long* ids, const float* w, float* out, long long T, int d, int vocab, void* stream);
+int b200_embedding_bwd(const long long* ids, const float* dout, float* dw, long long T, int d, int vocab,
+                       int zero_first, void* stream);
+int b200_cast_f32_to_bf16(const float* in, void* out, long long n, void* stream);
+
+/* ---- softmax cross-entropy -------------------------------------------------------------------
+ * ref: cs336_basics/nn_utils.py:9-17. */
+int b200_xent_fwd(const void* logits, int dtype, const long long* targets, float* row_loss, float* lse, float* loss,
+                  int T, int V, int ld, void* stream);
+int b200_xent_bwd(const void* logits, int dtype, const long long* targets, const float* lse, const float* dloss,
+                  void* dlogits, int T, int V, int ld, int ld_out, void* stream);
+
+/* ---- multi-tensor AdamW / gradient clipping ----------------------------------------------------
+ * ref: cs336_basics/optimizer.py:50-86 and nn_utils.py:20-30 (per-tensor Python loops). */
+typedef struct {
+  float* p;
+  const float* g;
+  float* m;
+  float* v;
+  void* shadow_bf16; /* nullable: bf16 copy of p refreshed by the update */
+  long long n;
+  int aligned16; /* all pointers 16-byte aligned */
+  int pad_;
+} b200_adamw_tensor;
+int b200_adamw_chunk_elems(void);
+/* hyper_dev: [lr, beta1, beta2, eps, weight_decay, grad_scale]; mode 0 = course AdamW, 1 = torch.optim.AdamW */
+int b200_adamw_multi(const b200_adamw_tensor* table_dev, const long long* chunk_start_dev, int n_tensors,
+                     long long total_chunks, const float* hyper_dev, int* step_dev, int mode, int increment_step,
+                     void* stream);
+int b200_gradnorm_partials(long long total_chunks);
+int b200_clip_grad_norm(const b200_adamw_tensor* table_dev, const long long* chunk_start_dev, int n_tensors,
+                        long long total_chunks, float max_norm, float eps, float* partial_dev, float* norm_out_dev,
+                        int apply_scale, void* stream);
+
+/* ---- NVLink symmetric-memory collectives -------------------------------------------------------
+ * peer_ptrs_dev: device array of world_size base pointers of the symmetric arena (peer-mapped);
+ * signal_ptrs_dev: device array of world_size signal-pad pointers; byte_off selects the bucket.
+ * The buffer is averaged in place on every rank (sum over ranks × scale).
+ * algo: 0 auto, 1 one-shot, 2 two-shot, 3 multimem (needs multicast_ptr != 0).
+ * ref: dist.all_reduce(...) + grad/world_size (ddp_bucketed_overlapped_sharded.py:236,247,299,314). */
+int b200_allreduce(void* const* peer_ptrs_dev, unsigned int* const* signal_ptrs_dev, void* multicast_ptr,
+                   long long byte_off, long long numel, int dtype, float scale, int rank, int world_size, int algo,
+                   int blocks, int signal_slot, void* stream);
+/* Owner-rank AdamW on [elem_off, elem_off+n) of the parameter arena fused with the P2P store of the
+ * new values into every peer's parameter arena (and bf16 shadow arena when given).
+ * ref: local optimizer.step + per-parameter dist.broadcast (…sharded.py:335-340). */
+int b200_adamw_shard_distribute(float* const* param_peer_ptrs_dev, void* const* shadow_peer_ptrs_dev /*nullable*/,
+                                const float* grad, float* m, float* v, long long elem_off, long long n,
+                                const float* hyper_dev, const int* step_dev, int mode, int world_size, int blocks,
+                                void* stream);
+/* Cross-rank barrier on the signal pads (used after the distribute so peers see the stores). */
+int b200_symm_barrier(unsigned int* const* signal_ptrs_dev, int rank, int world_size, int signal_slot, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SYS_H_ */

@@ -1,0 +1,93 @@
+"""End-to-end LM on the native sm_100a path vs. the PyTorch oracle path (same weights)."""
+import copy
+import os
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from cs336_a2_systems_b200.models import TransformerLM  # noqa: E402
+from cs336_a2_systems_b200.ops import cross_entropy  # noqa: E402
+from cs336_a2_systems_b200.optim import AdamW  # noqa: E402
+
+
+def _rel(a, b):
+    return float((a.float() - b.float()).norm() / (b.float().norm() + 1e-12))
+
+
+def _model(d_model=256, heads=4, layers=2, d_ff=512, vocab=1000, ctx=256):
+    torch.manual_seed(0)
+    return TransformerLM(vocab_size=vocab, context_length=ctx, d_model=d_model, num_layers=layers,
+                         num_heads=heads, d_ff=d_ff, rope_theta=10000.0).cuda()
+
+
+def _oracle_step(model, x, y):
+    os.environ["B200SYS_FORCE_TORCH"] = "1"
+    try:
+        logits = model(x)  # fp32, plain PyTorch ops
+        loss = torch.nn.functional.cross_entropy(logits.view(-1, logits.shape[-1]).float(), y.view(-1))
+        loss.backward()
+    finally:
+        os.environ["B200SYS_FORCE_TORCH"] = "0"
+    return logits.detach(), loss.detach()
+
+
+@pytest.mark.parametrize("cfg", [dict(), dict(d_model=320, heads=4, d_ff=832)])  # head dim 64 and 80
+def test_native_lm_matches_oracle(cfg):
+    native = _model(**cfg)
+    oracle = copy.deepcopy(native)
+    x = torch.randint(0, 1000, (2, 256), device="cuda")
+    y = torch.randint(0, 1000, (2, 256), device="cuda")
+    ref_logits, ref_loss = _oracle_step(oracle, x, y)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        logits = native(x)
+        loss = cross_entropy(logits, y)
+    loss.backward()
+    assert logits.dtype == torch.bfloat16
+    assert _rel(logits, ref_logits) < 3e-2
+    assert abs(float(loss) - float(ref_loss)) < 3e-2
+    for (n, p), q in zip(native.named_parameters(), oracle.parameters()):
+        assert p.grad is not None, n
+        assert p.grad.dtype == torch.float32
+        assert _rel(p.grad, q.grad) < 8e-2, f"{n}: {_rel(p.grad, q.grad)}"
+
+
+def test_native_training_reduces_loss_and_refreshes_shadows():
+    model = _model(layers=2)
+    opt = AdamW(model.parameters(), lr=3e-3, weight_decay=0.0)
+    x = torch.randint(0, 1000, (4, 128), device="cuda")
+    y = torch.roll(x, -1, dims=1)
+    losses = []
+    for _ in range(12):
+        opt.zero_grad()
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            loss = cross_entropy(model(x), y)
+        loss.backward()
+        opt.step()
+        losses.append(float(loss))
+    assert losses[-1] < losses[0] - 0.5, losses
+    # the fused optimizer keeps the bf16 GEMM operands in sync with the fp32 master weights
+    w = model.layers[0].ffn.w2.weight
+    from cs336_a2_systems_b200.ops import native
+    (sh,) = native.shadow_slices_of(w)
+    assert torch.equal(sh, w.detach().to(torch.bfloat16))
+
+
+def test_gradients_land_in_registered_slots():
+    from cs336_a2_systems_b200.ops import grad_slots
+    model = _model(layers=1)
+    params = [p for p in model.parameters()]
+    total = sum((p.numel() + 3) // 4 * 4 for p in params)
+    arena = torch.zeros(total, device="cuda")
+    off = 0
+    for p in params:
+        grad_slots.register(p, arena, off)
+        off += (p.numel() + 3) // 4 * 4
+    x = torch.randint(0, 1000, (2, 128), device="cuda")
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        cross_entropy(model(x), x).backward()
+    lo, hi = arena.data_ptr(), arena.data_ptr() + arena.numel() * 4
+    for n, p in model.named_parameters():
+        assert lo <= p.grad.data_ptr() < hi, f"{n} gradient was not produced into its slot"
+        grad_slots.unregister(p)
