@@ -1,0 +1,127 @@
+"""The training step: zero_grad → autocast forward → cross-entropy → backward (DDP hooks fire) →
+finish gradient sync → optional clip → optimizer step.
+
+Counterpart of the hot loops in the reference drivers
+(``ddp_bucketed_overlapped_sharded.py:161-197``, ``naive_ddp.py:53-171``, ``benchmark.py:89-117``).
+``Trainer.step_from_host`` is the end-to-end call a user makes: it stages the batch from pinned
+host memory, runs the step and returns the loss as a Python float (one 4-byte D2H read).
+
+With ``cuda_graph=True`` the whole step (forward, backward, reductions on their side stream,
+fused AdamW) is captured once into a CUDA graph and replayed — launch-bound Python/autograd
+overhead disappears; the step counter and hyper-parameters live in device memory so the replay
+stays exact (see ``optim/adamw.py``).
+"""
+
+from __future__ import annotations
+
+import contextlib
+
+import torch
+from torch import Tensor
+
+from ..ops import cross_entropy, grad_slots
+from ..ops.api import clip_gradient
+from ..utils import nvtx
+
+
+class GradArena:
+    """Flat fp32 gradient buffer for single-process training: registers one slot per parameter so
+    weight gradients are produced in place (stable addresses → CUDA-graph friendly, one flat
+    buffer for clipping / the fused optimizer)."""
+
+    def __init__(self, params, align_elems: int = 4):
+        self.params = [p for p in params if p.requires_grad]
+        total = 0
+        self.offsets = []
+        for p in self.params:
+            self.offsets.append(total)
+            total += (p.numel() + align_elems - 1) // align_elems * align_elems
+        dev = self.params[0].device
+        self.flat = torch.zeros(total, dtype=torch.float32, device=dev)
+        for p, off in zip(self.params, self.offsets):
+            if p.dtype == torch.float32:
+                grad_slots.register(p, self.flat, off)
+
+    def release(self):
+        grad_slots.release_all(self.params)
+
+
+class Trainer:
+    def __init__(self, model: torch.nn.Module, optimizer: torch.optim.Optimizer, *, autocast: bool = True,
+                 max_grad_norm: float | None = None, cuda_graph: bool = False, grad_arena: bool | None = None):
+        self.model = model
+        self.optimizer = optimizer
+        self.autocast = autocast
+        self.max_grad_norm = max_grad_norm
+        self.cuda_graph = cuda_graph
+        self.device = next(model.parameters()).device
+        self._is_ddp = hasattr(model, "finish_gradient_synchronization")
+        self.arena = None
+        if grad_arena or (grad_arena is None and self.device.type == "cuda" and not self._is_ddp):
+            self.arena = GradArena(list(model.parameters()))
+        self._graph = None
+        self._static_x = self._static_y = self._static_loss = None
+        self._warm_steps = 0
+        self.steps_done = 0
+
+    # ------------------------------------------------------------------ one eager step
+    def _ctx(self):
+        if self.autocast and self.device.type == "cuda":
+            return torch.autocast("cuda", dtype=torch.bfloat16)
+        return contextlib.nullcontext()
+
+    def _step_eager(self, x: Tensor, y: Tensor) -> Tensor:
+        if self._is_ddp and hasattr(self.model, "on_train_batch_start"):
+            self.model.on_train_batch_start()
+        if self.arena is not None:
+            self.arena.release()
+        self.optimizer.zero_grad(set_to_none=True)
+        with nvtx.range("forward"), self._ctx():
+            logits = self.model(x)
+            loss = cross_entropy(logits, y)
+        with nvtx.range("backward"):
+            loss.backward()
+        if self._is_ddp:
+            with nvtx.range("grad_sync"):
+                self.model.finish_gradient_synchronization()
+        if self.max_grad_norm is not None:
+            clip_gradient(self.model.parameters(), self.max_grad_norm)
+        with nvtx.range("optimizer"):
+            self.optimizer.step()
+        return loss.detach()
+
+    # ------------------------------------------------------------------ CUDA-graph step
+    def _capture(self, x: Tensor, y: Tensor) -> None:
+        self._static_x = x.clone()
+        self._static_y = y.clone()
+        self._graph = torch.cuda.CUDAGraph()
+        # private side stream for capture, as torch requires
+        s = torch.cuda.Stream(device=self.device)
+        s.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(s):
+            self.optimizer.zero_grad(set_to_none=True)
+            with torch.cuda.graph(self._graph, stream=s):
+                self._static_loss = self._step_eager(self._static_x, self._static_y)
+        torch.cuda.current_stream(self.device).wait_stream(s)
+
+    def step(self, x: Tensor, y: Tensor) -> Tensor:
+        """One optimisation step on device-resident ``x, y`` (int64 ``[B, S]``). Returns the loss tensor."""
+        self.steps_done += 1
+        if not self.cuda_graph or self.device.type != "cuda":
+            return self._step_eager(x, y)
+        if self._graph is None:
+            if self._warm_steps < 3:  # plans, shadows and allocator pools must exist before capture
+                self._warm_steps += 1
+                return self._step_eager(x, y)
+            self._capture(x, y)
+            # the capture itself does not execute; fall through to a replay for this step
+        self._static_x.copy_(x, non_blocking=True)
+        self._static_y.copy_(y, non_blocking=True)
+        self._graph.replay()
+        return self._static_loss
+
+    def step_from_host(self, x_host: Tensor, y_host: Tensor) -> float:
+        """End-to-end step: pinned-host batch → device, train step, loss back to the host."""
+        x = x_host.to(self.device, non_blocking=True)
+        y = y_host.to(self.device, non_blocking=True)
+        return float(self.step(x, y).item())
