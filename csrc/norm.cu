@@ -6,6 +6,8 @@
 // activations for the next GEMM and the per-row rstd.  fp32 math throughout.
 #include "common.cuh"
 
+#include <mutex>
+
 namespace b200 {
 
 template <typename T> __device__ __forceinline__ float ld_as_float(const T* p, size_t i);
@@ -215,4 +217,72 @@ extern "C" int b200_residual_add(const float* x, const void* y_bf16, float* out,
       x, reinterpret_cast<const __nv_bfloat16*>(y_bf16), out, (size_t)n);
   B200_LAUNCH_CHECK();
   return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Allocation-free variant of b200_rmsnorm_bwd.
+//
+// Who needs it: callers that are not allowed to create device allocations while they run — a host
+// application whose whole device-memory budget was handed to its own pool at start-up (so a foreign
+// library calling cudaMalloc could fail or fragment it), a latency-critical loop that cannot afford
+// the implicit device-wide synchronisation of cudaMalloc/cudaFree, or a plug-in ABI that gives a
+// library input and output buffers and nothing else.  b200_rmsnorm_bwd asks such a caller for a
+// scratch buffer of workspace_rows(T) * d floats; this variant keeps that scratch inside the library
+// image instead, in the fixed-size array below.
+//
+// Cost and limits: the array (B200_RMSNORM_BWD_NOALLOC_MAX_FLOATS floats, 4.75 MiB) is part of the
+// module, so every GPU that loads libb200sys holds it until the process exits.  Problems whose
+// partial-sum matrix does not fit are rejected with B200_ERR_ARG and a message; nothing is truncated.
+//
+// Sharing: all calls on a device use the same array.  The kernels overwrite every element they
+// later read (each CTA stores a full d-wide row of partial sums before the column reduction runs),
+// so nothing has to be cleared between calls and stale contents from an earlier call are harmless.
+// Two calls that overlap on the GPU (different streams, or the same entry point from two threads
+// without ordering) race on the array — serialise them.
+//
+// Set-up: in host code the array's name is only a stand-in for the symbol, not a device address.
+// The first call on each device, made with that device current, resolves the real address with
+// cudaGetSymbolAddress and caches it; make that first call before starting any stream capture.
+// The entry point calls no cudaMalloc/cudaFree and no allocating library routine.
+// ------------------------------------------------------------------------------------------------
+#define B200_RMSNORM_BWD_NOALLOC_MAX_FLOATS (304 * 4096)
+
+static __device__ __align__(256) float g_rmsnorm_bwd_static_scratch[B200_RMSNORM_BWD_NOALLOC_MAX_FLOATS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+float* g_static_scratch_addr[kMaxDevices] = {nullptr};
+std::mutex g_static_scratch_mu;
+
+// Device address of the static scratch on the current device (resolved once per device).
+int static_scratch_for_current_device(float** out) {
+  int dev = -1;
+  B200_CHECK_CUDA(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < kMaxDevices, "rmsnorm_bwd_noalloc: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_static_scratch_mu);
+  if (g_static_scratch_addr[dev] == nullptr) {
+    float* ptr = nullptr;
+    B200_CHECK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_rmsnorm_bwd_static_scratch));
+    B200_REQUIRE(ptr != nullptr, "rmsnorm_bwd_noalloc: cudaGetSymbolAddress returned a null address");
+    g_static_scratch_addr[dev] = ptr;
+  }
+  *out = g_static_scratch_addr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" long long b200_rmsnorm_bwd_noalloc_max_floats(void) { return B200_RMSNORM_BWD_NOALLOC_MAX_FLOATS; }
+
+extern "C" int b200_rmsnorm_bwd_noalloc(const void* dy, int dy_dtype, const float* x, const float* w,
+                                        const float* rstd, const float* dres_in, float* dx, void* dx_bf16, float* dw,
+                                        int dw_accumulate, int T, int d, void* stream) {
+  B200_REQUIRE(T > 0 && d > 0, "rmsnorm_bwd_noalloc: empty input");
+  const long long need = (long long)b200_rmsnorm_bwd_workspace_rows(T) * d;
+  B200_REQUIRE(need <= (long long)B200_RMSNORM_BWD_NOALLOC_MAX_FLOATS,
+               "rmsnorm_bwd_noalloc: needs %lld floats of scratch (rows %d x d %d) but the built-in buffer holds %d; "
+               "use b200_rmsnorm_bwd with caller-provided scratch",
+               need, b200_rmsnorm_bwd_workspace_rows(T), d, (int)B200_RMSNORM_BWD_NOALLOC_MAX_FLOATS);
+  float* scratch = nullptr;
+  if (int rc = static_scratch_for_current_device(&scratch)) return rc;
+  return b200_rmsnorm_bwd(dy, dy_dtype, x, w, rstd, dres_in, dx, dx_bf16, dw, dw_accumulate, scratch, T, d, stream);
 }

@@ -58,6 +58,19 @@ int b200_rmsnorm_bwd_workspace_rows(int T);
 int b200_rmsnorm_bwd(const void* dy, int dy_dtype, const float* x, const float* w, const float* rstd,
                      const float* dres_in /*nullable*/, float* dx /*nullable*/, void* dx_bf16 /*nullable*/, float* dw,
                      int dw_accumulate, float* scratch /* workspace_rows(T)*d floats */, int T, int d, void* stream);
+/* Allocation-free variant of b200_rmsnorm_bwd (no counterpart in the reference: it is an addition of this
+ * library).  For callers that may not allocate device memory while running — a host whose memory budget is
+ * owned by its own pool, a loop that cannot take cudaMalloc's device-wide synchronisation, a plug-in ABI that
+ * passes inputs and outputs only.  The partial-sum scratch lives in a fixed array inside the library image
+ * (b200_rmsnorm_bwd_noalloc_max_floats() floats = 4.75 MiB, resident on every GPU that loads the library
+ * until exit); a problem with workspace_rows(T)*d beyond that is rejected with B200_ERR_ARG.  The first call
+ * on each device (with that device current) resolves the array's device address — make it before any stream
+ * capture.  All calls share the array: calls that overlap on the GPU race, serialise them.  Never calls
+ * cudaMalloc/cudaFree or an allocating library routine. */
+long long b200_rmsnorm_bwd_noalloc_max_floats(void);
+int b200_rmsnorm_bwd_noalloc(const void* dy, int dy_dtype, const float* x, const float* w, const float* rstd,
+                             const float* dres_in /*nullable*/, float* dx /*nullable*/, void* dx_bf16 /*nullable*/,
+                             float* dw, int dw_accumulate, int T, int d, void* stream);
 int b200_residual_add(const float* x, const void* y_bf16, float* out, long long n, void* stream);
 /* ref: RoPE model.py:135-147 (interleaved pairs); qkv is [B,S,3,H,dh] bf16, q and k rotated in place. */
 int b200_rope_qk_inplace(void* qkv_bf16, const float* cache /*(2,ctx,dh/2)*/, int ctx, int B, int S, int H, int dh,
