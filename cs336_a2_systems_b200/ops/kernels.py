@@ -334,13 +334,14 @@ def fa2_bwd(q, k, v, o, lse, do, causal: bool, dq=None, dk=None, dv=None):
 # ------------------------------------------------------------------------------------------------
 # NVLink collectives
 # ------------------------------------------------------------------------------------------------
-_signal_slot = 0
+def host_ptr_array(ptrs):
+    """ctypes array of device addresses (the C ABI takes peer tables as small host arrays)."""
+    return (ctypes.c_ulonglong * len(ptrs))(*[int(x) for x in ptrs])
 
 
 def allreduce_avg(arena, byte_off: int, numel: int, dtype: torch.dtype, one_shot_max: int, blocks: int,
-                  algo: int = 0) -> None:
+                  algo: int = 0, signal_slot: int = 0) -> None:
     """In-place average over ranks of ``numel`` elements at ``byte_off`` of the symmetric arena."""
-    global _signal_slot
     es = 2 if dtype == torch.bfloat16 else 4
     if algo == 0:
         if numel * es <= one_shot_max:
@@ -349,9 +350,26 @@ def allreduce_avg(arena, byte_off: int, numel: int, dtype: torch.dtype, one_shot
             algo = 3
         else:
             algo = 2
-    check(_lib().b200_allreduce(c_void_p(arena.peer_ptrs_dev), c_void_p(arena.signal_ptrs_dev),
-                                c_void_p(arena.multicast_ptr), c_longlong(byte_off), c_longlong(numel),
-                                c_int(_DT[dtype]), c_float(1.0 / arena.world_size), c_int(arena.rank),
-                                c_int(arena.world_size), c_int(algo), c_int(blocks), c_int(0), stream_ptr()),
-          "allreduce")
+    check(_lib().b200_allreduce(arena.peer_ptrs_c, arena.signal_ptrs_c, c_void_p(arena.multicast_ptr),
+                                c_longlong(byte_off), c_longlong(numel), c_int(_DT[dtype]),
+                                c_float(1.0 / arena.world_size), c_int(arena.rank), c_int(arena.world_size),
+                                c_int(algo), c_int(blocks), c_int(signal_slot), stream_ptr()), "allreduce")
     _count()
+
+
+def symm_barrier(arena, signal_slot: int) -> None:
+    check(_lib().b200_symm_barrier(arena.signal_ptrs_c, c_int(arena.rank), c_int(arena.world_size),
+                                   c_int(signal_slot), stream_ptr()), "symm_barrier")
+    _count()
+
+
+def adamw_multi_distribute(launch: "AdamWLaunch", param_arena, shadow_arena) -> None:
+    """Owner AdamW over ``launch``'s table + P2P store of the new values into every rank's arenas."""
+    check(_lib().b200_adamw_multi_distribute(
+        p(launch.tt.table), p(launch.tt.starts), c_int(launch.tt.n), c_longlong(launch.tt.total_chunks),
+        p(launch.hyper), p(launch.step), c_int(launch.mode), c_int(1), param_arena.peer_ptrs_c,
+        shadow_arena.peer_ptrs_c if shadow_arena is not None else None,
+        ctypes.c_ulonglong(param_arena.bytes.data_ptr()),
+        ctypes.c_ulonglong(shadow_arena.bytes.data_ptr() if shadow_arena is not None else 0),
+        c_int(param_arena.world_size), stream_ptr()), "adamw_multi_distribute")
+    _count(2)

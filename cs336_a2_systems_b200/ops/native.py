@@ -34,6 +34,24 @@ class _ShadowEntry:
         self.tensor, self.versions, self.row_offsets = tensor, versions, row_offsets
 
 
+_shadow_provider = None
+
+
+def set_shadow_provider(fn) -> None:
+    """``fn(weights) -> bf16 [ΣN, K] tensor | None``: lets an owner of special memory (the NVLink
+    symmetric shadow arena of the fused sharded optimizer) supply the storage of new shadows."""
+    global _shadow_provider
+    _shadow_provider = fn
+
+
+def drop_shadows(params) -> None:
+    """Forget cached shadows of ``params`` (they are rebuilt, through the provider, on next use)."""
+    for w in params:
+        for attr in ("_b200_shadows", "_b200_shadow_slices"):
+            if hasattr(w, attr):
+                delattr(w, attr)
+
+
 def _shadow_entry(weights: tuple[Tensor, ...]) -> _ShadowEntry:
     key = tuple(id(w) for w in weights)
     w0 = weights[0]
@@ -49,7 +67,10 @@ def _shadow_entry(weights: tuple[Tensor, ...]) -> _ShadowEntry:
             assert w.dim() == 2 and w.shape[1] == K and w.dtype == torch.float32
             offs.append(n)
             n += w.shape[0]
-        ent = _ShadowEntry(torch.empty(n, K, dtype=BF16, device=w0.device), [None] * len(weights), offs)
+        buf = _shadow_provider(weights) if _shadow_provider is not None else None
+        if buf is None:
+            buf = torch.empty(n, K, dtype=BF16, device=w0.device)
+        ent = _ShadowEntry(buf, [None] * len(weights), offs)
         reg[key] = ent
         for i, w in enumerate(weights):  # let the optimizer find the slice it must keep fresh
             lst = getattr(w, "_b200_shadow_slices", None)

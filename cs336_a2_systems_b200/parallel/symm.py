@@ -28,6 +28,7 @@ import torch.distributed as dist
 
 _ONE_SHOT_MAX_BYTES = int(os.environ.get("B200SYS_ONESHOT_MAX", 512 * 1024))
 _COMM_BLOCKS = int(os.environ.get("B200SYS_COMM_BLOCKS", 16))
+_ALGO = int(os.environ.get("B200SYS_ALLREDUCE_ALGO", 0))  # 0 auto, 1 one-shot, 2 two-shot, 3 multimem
 
 
 def is_legal(devices, dtypes, group) -> tuple[bool, str]:
@@ -73,9 +74,16 @@ class SymmArena:
         self.bytes = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
         self.bytes.zero_()
         self.handle = symm_mem.rendezvous(self.bytes, self.group.group_name)
-        self.peer_ptrs_dev = int(self.handle.buffer_ptrs_dev)
-        self.signal_ptrs_dev = int(self.handle.signal_pad_ptrs_dev)
-        self.peer_ptrs = list(self.handle.buffer_ptrs)
+        from ..ops import kernels
+
+        self.peer_ptrs = [int(x) for x in self.handle.buffer_ptrs]
+        self.signal_ptrs = [int(x) for x in self.handle.signal_pad_ptrs]
+        self.peer_ptrs_c = kernels.host_ptr_array(self.peer_ptrs)
+        self.signal_ptrs_c = kernels.host_ptr_array(self.signal_ptrs)
+        need = 2 * 4 * kernels._lib().b200_comm_signal_words()  # two signal slots of 32-bit words
+        pad = int(getattr(self.handle, "signal_pad_size", need))
+        if pad < need:
+            raise RuntimeError(f"symmetric-memory signal pad too small: {pad} < {need} bytes")
         try:
             self.multicast_ptr = int(self.handle.multicast_ptr)
         except Exception:  # pragma: no cover
@@ -126,7 +134,7 @@ class SymmReducer:
         self.stream.wait_event(ev)
         with torch.cuda.stream(self.stream):
             kernels.allreduce_avg(self.arena, self._offs[bi], self._numels[bi], self._dtypes[bi],
-                                  one_shot_max=_ONE_SHOT_MAX_BYTES, blocks=_COMM_BLOCKS)
+                                  one_shot_max=_ONE_SHOT_MAX_BYTES, blocks=_COMM_BLOCKS, algo=_ALGO)
         return bi
 
     def reduce_bucket_async(self, bi: int):

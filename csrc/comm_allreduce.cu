@@ -1,0 +1,243 @@
+// Gradient all-reduce over NVLink 5 / NVSwitch peer memory, fused with the 1/world_size average.
+//
+// Replaces dist.all_reduce(...) + grad/world_size of the reference's DDP classes
+// (cs336_systems/ddp_bucketed_overlapped_sharded.py:236,247,299,314) and the NCCL ring behind them.
+// Every rank passes the peer-mapped base pointers of a symmetric arena (set up
+// through torch.distributed._symmetric_memory) — as a small host array that travels to the kernel by value; the kernels load and store peer memory directly.
+//
+//   one-shot  : every rank loads all ranks' copies of the whole message, reduces in rank order in
+//               registers, cross-rank barrier, writes its own copy.  One NVLink traversal; for small
+//               messages (latency bound).
+//   two-shot  : rank r reduces slice r (peer loads) and stores the averaged slice into every rank's
+//               buffer (peer stores).  2·(ws-1)/ws·S bytes per GPU each way.
+//   multimem  : slice r is reduced INSIDE the switch with multimem.ld_reduce on the NVLS multicast
+//               address and broadcast with multimem.st — ≈S/ws loads + S/ws stores per GPU.
+//
+// Cross-rank ordering: CTA b of every rank meets CTA b of every other rank through flag words in the
+// signal pads (put = CAS 0→1 release.sys on the peer's pad, wait = CAS 1→0 acquire.sys on ours), once
+// before the first peer access and once after the last; no host involvement.  The reduction order is
+// fixed (rank 0..ws-1, or the switch's), and each element is produced by exactly one rank in the
+// two-shot / multimem variants, so all replicas end bit-identical.
+#include "common.cuh"
+
+namespace b200 {
+namespace comm {
+
+constexpr int kMaxRanks = 8;
+constexpr int kThreads = 512;
+constexpr int kMaxBlocks = 32;
+
+struct Peers {
+  void* ptr[kMaxRanks];
+  unsigned int* sig[kMaxRanks];
+};
+
+__device__ __forceinline__ unsigned cas_release_sys(unsigned* addr, unsigned cmp, unsigned val) {
+  unsigned old;
+  asm volatile("atom.global.release.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(addr), "r"(cmp), "r"(val) : "memory");
+  return old;
+}
+__device__ __forceinline__ unsigned cas_acquire_sys(unsigned* addr, unsigned cmp, unsigned val) {
+  unsigned old;
+  asm volatile("atom.global.acquire.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(addr), "r"(cmp), "r"(val) : "memory");
+  return old;
+}
+
+// CTA-to-CTA barrier across ranks (same blockIdx on every rank).  Reusable: every flag returns to 0.
+__device__ __forceinline__ void cross_rank_barrier(const Peers& P, int rank, int ws, int slot) {
+  __syncthreads();
+  if (threadIdx.x < ws) {
+    const int peer = threadIdx.x;
+    unsigned* send = P.sig[peer] + slot + blockIdx.x * kMaxRanks + rank;
+    unsigned* recv = P.sig[rank] + slot + blockIdx.x * kMaxRanks + peer;
+    while (cas_release_sys(send, 0u, 1u) != 0u) {
+    }
+    while (cas_acquire_sys(recv, 1u, 0u) != 1u) {
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ f32x4 ld_peer(const void* p) {
+  f32x4 v;
+  asm volatile("ld.global.relaxed.sys.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_peer(void* p, const f32x4& v) {
+  asm volatile("st.global.relaxed.sys.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// 16-byte vector arithmetic for the two element types
+template <bool BF16> struct Vec;
+template <> struct Vec<false> {
+  static __device__ __forceinline__ void add(float (&acc)[8], const f32x4& v) { acc[0] += v.x; acc[1] += v.y; acc[2] += v.z; acc[3] += v.w; }
+  static __device__ __forceinline__ f32x4 finish(const float (&acc)[8], float s) { return f32x4{acc[0] * s, acc[1] * s, acc[2] * s, acc[3] * s}; }
+};
+template <> struct Vec<true> {
+  static __device__ __forceinline__ void add(float (&acc)[8], const f32x4& v) {
+    const uint32_t* u = reinterpret_cast<const uint32_t*>(&v);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { const float2 f = unpack_bf16x2(u[k]); acc[2 * k] += f.x; acc[2 * k + 1] += f.y; }
+  }
+  static __device__ __forceinline__ f32x4 finish(const float (&acc)[8], float s) {
+    f32x4 o;
+    uint32_t* u = reinterpret_cast<uint32_t*>(&o);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) u[k] = pack_bf16x2(acc[2 * k] * s, acc[2 * k + 1] * s);
+    return o;
+  }
+};
+
+// ---- one-shot --------------------------------------------------------------------------------
+constexpr int kOneShotVecs = 8;  // 16-byte vectors held per thread across the barrier
+
+template <bool BF16>
+__global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(Peers P, long long byte_off, long long nvec,
+                                                                     float scale, int rank, int ws, int slot) {
+  cross_rank_barrier(P, rank, ws, slot);
+  f32x4 res[kOneShotVecs];
+  const long long stride = (long long)gridDim.x * kThreads;
+  const long long i0 = (long long)blockIdx.x * kThreads + threadIdx.x;
+#pragma unroll
+  for (int k = 0; k < kOneShotVecs; ++k) {
+    const long long i = i0 + k * stride;
+    if (i < nvec) {
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      for (int r = 0; r < ws; ++r) Vec<BF16>::add(acc, ld_peer(static_cast<const char*>(P.ptr[r]) + byte_off + i * 16));
+      res[k] = Vec<BF16>::finish(acc, scale);
+    }
+  }
+  cross_rank_barrier(P, rank, ws, slot);  // everyone has read every copy: safe to overwrite ours
+  char* mine = static_cast<char*>(P.ptr[rank]) + byte_off;
+#pragma unroll
+  for (int k = 0; k < kOneShotVecs; ++k) {
+    const long long i = i0 + k * stride;
+    if (i < nvec) *reinterpret_cast<f32x4*>(mine + i * 16) = res[k];
+  }
+}
+
+// ---- two-shot --------------------------------------------------------------------------------
+template <bool BF16>
+__global__ void __launch_bounds__(kThreads) allreduce_twoshot_kernel(Peers P, long long byte_off, long long nvec,
+                                                                     float scale, int rank, int ws, int slot) {
+  cross_rank_barrier(P, rank, ws, slot);
+  const long long per = (nvec + ws - 1) / ws;
+  const long long lo = per * rank, hi = (lo + per < nvec) ? lo + per : nvec;
+  for (long long i = lo + (long long)blockIdx.x * kThreads + threadIdx.x; i < hi; i += (long long)gridDim.x * kThreads) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    f32x4 v[kMaxRanks];
+#pragma unroll
+    for (int r = 0; r < kMaxRanks; ++r)
+      if (r < ws) v[r] = ld_peer(static_cast<const char*>(P.ptr[r]) + byte_off + i * 16);
+#pragma unroll
+    for (int r = 0; r < kMaxRanks; ++r)
+      if (r < ws) Vec<BF16>::add(acc, v[r]);
+    const f32x4 out = Vec<BF16>::finish(acc, scale);
+#pragma unroll
+    for (int r = 0; r < kMaxRanks; ++r)
+      if (r < ws) st_peer(static_cast<char*>(P.ptr[r]) + byte_off + i * 16, out);
+  }
+  cross_rank_barrier(P, rank, ws, slot);  // all slices have landed everywhere
+}
+
+// ---- NVLS multimem -----------------------------------------------------------------------------
+template <bool BF16>
+__global__ void __launch_bounds__(kThreads) allreduce_multimem_kernel(Peers P, char* mc, long long byte_off,
+                                                                      long long nvec, float scale, int rank, int ws,
+                                                                      int slot) {
+  cross_rank_barrier(P, rank, ws, slot);
+  const long long per = (nvec + ws - 1) / ws;
+  const long long lo = per * rank, hi = (lo + per < nvec) ? lo + per : nvec;
+  for (long long i = lo + (long long)blockIdx.x * kThreads + threadIdx.x; i < hi; i += (long long)gridDim.x * kThreads) {
+    char* a = mc + byte_off + i * 16;
+    if constexpr (!BF16) {
+      float x, y, z, w;
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                   : "=f"(x), "=f"(y), "=f"(z), "=f"(w) : "l"(a) : "memory");
+      x *= scale; y *= scale; z *= scale; w *= scale;
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(a), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+    } else {
+      uint32_t u[4];
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                   : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]) : "l"(a) : "memory");
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { const float2 f = unpack_bf16x2(u[k]); u[k] = pack_bf16x2(f.x * scale, f.y * scale); }
+      asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};" ::"l"(a), "r"(u[0]), "r"(u[1]), "r"(u[2]), "r"(u[3]) : "memory");
+    }
+  }
+  cross_rank_barrier(P, rank, ws, slot);
+}
+
+__global__ void barrier_kernel(Peers P, int rank, int ws, int slot) { cross_rank_barrier(P, rank, ws, slot); }
+
+static int load_peers(const unsigned long long* peer_ptrs_host, const unsigned long long* signal_ptrs_host, int ws,
+                      Peers* out) {
+  for (int r = 0; r < kMaxRanks; ++r) {
+    out->ptr[r] = (r < ws && peer_ptrs_host) ? reinterpret_cast<void*>(peer_ptrs_host[r]) : nullptr;
+    out->sig[r] = (r < ws && signal_ptrs_host) ? reinterpret_cast<unsigned int*>(signal_ptrs_host[r]) : nullptr;
+  }
+  for (int r = 0; r < ws; ++r)
+    if (!out->sig[r]) { set_error("comm: null signal-pad pointer for rank %d", r); return B200_ERR_ARG; }
+  return 0;
+}
+
+}  // namespace comm
+}  // namespace b200
+
+using namespace b200;
+using namespace b200::comm;
+
+extern "C" int b200_allreduce(const unsigned long long* peer_ptrs_host, const unsigned long long* signal_ptrs_host,
+                              void* multicast_ptr,
+                              long long byte_off, long long numel, int dtype, float scale, int rank, int world_size,
+                              int algo, int blocks, int signal_slot, void* stream) {
+  B200_REQUIRE(world_size >= 1 && world_size <= kMaxRanks, "allreduce: world size %d unsupported (1..8)", world_size);
+  B200_REQUIRE(dtype == B200_F32 || dtype == B200_BF16, "allreduce: dtype must be fp32 or bf16");
+  B200_REQUIRE(byte_off % 16 == 0, "allreduce: buffer offset must be 16-byte aligned");
+  if (numel <= 0) return 0;
+  const int es = dtype == B200_F32 ? 4 : 2;
+  const long long nbytes = numel * es;
+  const long long nvec = (nbytes + 15) / 16;  // buckets are padded to 16 bytes by the allocator
+  Peers P;
+  if (int rc = load_peers(peer_ptrs_host, signal_ptrs_host, world_size, &P)) return rc;
+  if (blocks <= 0) blocks = 16;
+  if (blocks > kMaxBlocks) blocks = kMaxBlocks;
+  const long long want = (nvec + kThreads - 1) / kThreads;
+  if (want < blocks) blocks = (int)(want < 1 ? 1 : want);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (algo == 0) algo = nbytes <= 256 * 1024 ? 1 : (multicast_ptr ? 3 : 2);
+  if (algo == 1 && nvec > (long long)blocks * kThreads * kOneShotVecs) algo = 2;  // does not fit in registers
+  if (algo == 3 && !multicast_ptr) algo = 2;
+  const bool bf = dtype == B200_BF16;
+  switch (algo) {
+    case 1:
+      if (bf) allreduce_oneshot_kernel<true><<<blocks, kThreads, 0, s>>>(P, byte_off, nvec, scale, rank, world_size, signal_slot);
+      else allreduce_oneshot_kernel<false><<<blocks, kThreads, 0, s>>>(P, byte_off, nvec, scale, rank, world_size, signal_slot);
+      break;
+    case 2:
+      if (bf) allreduce_twoshot_kernel<true><<<blocks, kThreads, 0, s>>>(P, byte_off, nvec, scale, rank, world_size, signal_slot);
+      else allreduce_twoshot_kernel<false><<<blocks, kThreads, 0, s>>>(P, byte_off, nvec, scale, rank, world_size, signal_slot);
+      break;
+    case 3:
+      if (bf) allreduce_multimem_kernel<true><<<blocks, kThreads, 0, s>>>(P, static_cast<char*>(multicast_ptr), byte_off, nvec, scale, rank, world_size, signal_slot);
+      else allreduce_multimem_kernel<false><<<blocks, kThreads, 0, s>>>(P, static_cast<char*>(multicast_ptr), byte_off, nvec, scale, rank, world_size, signal_slot);
+      break;
+    default:
+      set_error("allreduce: unknown algorithm %d", algo);
+      return B200_ERR_ARG;
+  }
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200_symm_barrier(const unsigned long long* signal_ptrs_host, int rank, int world_size, int signal_slot,
+                                 void* stream) {
+  B200_REQUIRE(world_size >= 1 && world_size <= kMaxRanks, "symm_barrier: world size %d unsupported", world_size);
+  Peers P;
+  if (int rc = load_peers(nullptr, signal_ptrs_host, world_size, &P)) return rc;
+  barrier_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(P, rank, world_size, signal_slot);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200_comm_signal_words(void) { return kMaxBlocks * kMaxRanks; }

@@ -114,23 +114,30 @@ int b200_clip_grad_norm(const b200_adamw_tensor* table_dev, const long long* chu
                         int apply_scale, void* stream);
 
 /* ---- NVLink symmetric-memory collectives -------------------------------------------------------
- * peer_ptrs_dev: device array of world_size base pointers of the symmetric arena (peer-mapped);
- * signal_ptrs_dev: device array of world_size signal-pad pointers; byte_off selects the bucket.
- * The buffer is averaged in place on every rank (sum over ranks × scale).
- * algo: 0 auto, 1 one-shot, 2 two-shot, 3 multimem (needs multicast_ptr != 0).
+ * peer_ptrs_host / signal_ptrs_host: HOST arrays of world_size device addresses — the peer-mapped base of the
+ * symmetric arena and of its signal pad on every rank (from torch.distributed._symmetric_memory); byte_off
+ * selects the bucket.  The buffer is averaged in place on every rank (sum over ranks x scale).
+ * algo: 0 auto, 1 one-shot, 2 two-shot, 3 multimem (needs multicast_ptr != 0).  Uses
+ * b200_comm_signal_words() 32-bit words of the signal pad starting at signal_slot.
  * ref: dist.all_reduce(...) + grad/world_size (ddp_bucketed_overlapped_sharded.py:236,247,299,314). */
-int b200_allreduce(void* const* peer_ptrs_dev, unsigned int* const* signal_ptrs_dev, void* multicast_ptr,
-                   long long byte_off, long long numel, int dtype, float scale, int rank, int world_size, int algo,
-                   int blocks, int signal_slot, void* stream);
-/* Owner-rank AdamW on [elem_off, elem_off+n) of the parameter arena fused with the P2P store of the
- * new values into every peer's parameter arena (and bf16 shadow arena when given).
- * ref: local optimizer.step + per-parameter dist.broadcast (…sharded.py:335-340). */
-int b200_adamw_shard_distribute(float* const* param_peer_ptrs_dev, void* const* shadow_peer_ptrs_dev /*nullable*/,
-                                const float* grad, float* m, float* v, long long elem_off, long long n,
-                                const float* hyper_dev, const int* step_dev, int mode, int world_size, int blocks,
-                                void* stream);
-/* Cross-rank barrier on the signal pads (used after the distribute so peers see the stores). */
-int b200_symm_barrier(unsigned int* const* signal_ptrs_dev, int rank, int world_size, int signal_slot, void* stream);
+int b200_comm_signal_words(void);
+int b200_allreduce(const unsigned long long* peer_ptrs_host, const unsigned long long* signal_ptrs_host,
+                   void* multicast_ptr, long long byte_off, long long numel, int dtype, float scale, int rank,
+                   int world_size, int algo, int blocks, int signal_slot, void* stream);
+/* Cross-rank barrier on the signal pads (orders peer stores before what follows on every rank). */
+int b200_symm_barrier(const unsigned long long* signal_ptrs_host, int rank, int world_size, int signal_slot,
+                      void* stream);
+/* Owner-rank multi-tensor AdamW fused with the distribution of the new values: table[i].p points into this
+ * rank's parameter arena (base local_param_base); the update is stored at the same offset of EVERY rank's
+ * arena (param_peer_bases_host) and, when given, its bf16 copy at the same offset of every rank's shadow arena.
+ * Follow with b200_symm_barrier before parameters are read.
+ * ref: local optimizer.step + one dist.broadcast per parameter (...sharded.py:335-340). */
+int b200_adamw_multi_distribute(const b200_adamw_tensor* table_dev, const long long* chunk_start_dev, int n_tensors,
+                                long long total_chunks, const float* hyper_dev, int* step_dev, int mode,
+                                int increment_step, const unsigned long long* param_peer_bases_host,
+                                const unsigned long long* shadow_peer_bases_host /*nullable*/,
+                                unsigned long long local_param_base, unsigned long long local_shadow_base,
+                                int world_size, void* stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,112 @@
+"""Multi-GPU (>= 2 B200) tests of the NVLink path: all-reduce kernels vs NCCL, DDP with arena-backed
+buckets vs the c10d backend, fused sharded AdamW vs the unsharded optimizer."""
+import os
+
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+
+from cs336_a2_systems_b200.parallel import find_free_port  # noqa: E402
+
+
+def _init(rank, ws, port):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=ws, device_id=torch.device("cuda", rank))
+    return torch.device("cuda", rank)
+
+
+def _allreduce_worker(rank, ws, port):
+    import torch.distributed as dist
+    from cs336_a2_systems_b200.ops import kernels
+    from cs336_a2_systems_b200.parallel import symm
+    dev = _init(rank, ws, port)
+    sizes = [4, 1000, 64 * 1024, 1 << 20, (1 << 22) + 12]
+    arena = symm.SymmArena(sum((n * 4 + 255) // 256 * 256 for n in sizes) * 2, dev, None)
+    algos = [1, 2] + ([3] if arena.multicast_ptr else [])
+    for dtype in (torch.float32, torch.bfloat16):
+        for algo in algos:
+            off = 0
+            for n in sizes:
+                torch.manual_seed(100 * rank + n % 97)
+                src = torch.randn(n, device=dev).to(dtype)
+                buf = arena.view(off, n, dtype)
+                buf.copy_(src)
+                ref = src.float().clone()
+                dist.all_reduce(ref)
+                ref /= ws
+                torch.cuda.synchronize()
+                dist.barrier()
+                kernels.allreduce_avg(arena, off, n, dtype, one_shot_max=0, blocks=16, algo=algo)
+                kernels.allreduce_avg(arena, off, n, dtype, one_shot_max=0, blocks=16, algo=algo)  # idempotent on equal replicas
+                torch.cuda.synchronize()
+                tol = 1e-5 if dtype == torch.float32 else 2e-2
+                torch.testing.assert_close(buf.float(), ref, rtol=tol, atol=tol, msg=f"algo {algo} n {n} {dtype}")
+                # replicas bit-identical
+                gathered = [torch.empty_like(buf) for _ in range(ws)]
+                dist.all_gather(gathered, buf.clone())
+                assert all(torch.equal(g, gathered[0]) for g in gathered)
+                off += (n * 4 + 255) // 256 * 256
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_allreduce_kernels_match_nccl():
+    ws = min(torch.cuda.device_count(), 8)
+    mp.spawn(_allreduce_worker, args=(ws, find_free_port()), nprocs=ws, join=True)
+
+
+def _ddp_worker(rank, ws, port):
+    import copy
+    import torch.distributed as dist
+    from cs336_a2_systems_b200.models import TransformerLM
+    from cs336_a2_systems_b200.ops import cross_entropy
+    from cs336_a2_systems_b200.optim import AdamW
+    from cs336_a2_systems_b200.parallel import DDPBucketed, DDPIndividualParameters, ShardedOptimizer
+    dev = _init(rank, ws, port)
+    torch.manual_seed(0)
+    base = TransformerLM(vocab_size=512, context_length=128, d_model=128, num_layers=2, num_heads=2, d_ff=256).to(dev)
+    models = {"c10d": DDPBucketed(copy.deepcopy(base), 0.25, backend="c10d"),
+              "symm": DDPBucketed(copy.deepcopy(base), 0.25, backend="symm"),
+              "symm_ind": DDPIndividualParameters(copy.deepcopy(base), backend="symm"),
+              "symm_sharded": DDPBucketed(copy.deepcopy(base), 0.25, backend="symm")}
+    assert models["symm"]._reducer.kind == "symm"
+    opts = {k: AdamW(m.parameters(), lr=1e-3, weight_decay=0.1) for k, m in models.items() if k != "symm_sharded"}
+    sh = ShardedOptimizer(models["symm_sharded"].parameters(), AdamW, lr=1e-3, weight_decay=0.1)
+    assert sh.enable_symmetric(), "fused NVLink sharded AdamW should be legal here"
+    opts["symm_sharded"] = sh
+    g = torch.Generator().manual_seed(7 + rank)
+    for step in range(4):
+        x = torch.randint(0, 512, (2, 128), generator=g).to(dev)
+        y = torch.roll(x, -1, 1)
+        for k, m in models.items():
+            m.on_train_batch_start()
+            opts[k].zero_grad()
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                loss = cross_entropy(m(x), y)
+            loss.backward()
+            m.finish_gradient_synchronization()
+            opts[k].step()
+    torch.cuda.synchronize()
+    ref = dict(models["c10d"].module.named_parameters())
+    for k in ("symm", "symm_ind", "symm_sharded"):
+        for n, p in models[k].module.named_parameters():
+            torch.testing.assert_close(p, ref[n], rtol=2e-3, atol=2e-4, msg=f"{k}:{n}")
+        # replicas identical across ranks
+        for n, p in models[k].module.named_parameters():
+            gathered = [torch.empty_like(p) for _ in range(ws)]
+            dist.all_gather(gathered, p.detach().contiguous())
+            assert all(torch.equal(t, gathered[0]) for t in gathered), f"{k}:{n} differs across ranks"
+    n_state = len(sh.optimizer.state) if sh.optimizer is not None else 0
+    assert n_state < len(list(base.parameters()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_ddp_symm_backends_match_c10d():
+    ws = min(torch.cuda.device_count(), 8)
+    mp.spawn(_ddp_worker, args=(ws, find_free_port()), nprocs=ws, join=True)
