@@ -156,8 +156,11 @@ class CausalMultiHeadSelfAttention(nn.Module):
         if native_active(x) and token_positions is None:
             from ..ops import native
 
-            qkv = native.linear(x, (self.q_proj.weight, self.k_proj.weight, self.v_proj.weight))
-            o = native.attention_core(qkv.view(-1, S, 3, H, dh), self.positional_encoder._freq_cis_cache)
+            cache = self.positional_encoder._freq_cis_cache
+            # one GEMM for q,k,v; its epilogue applies RoPE to the q and k columns
+            qkv = native.linear(x, (self.q_proj.weight, self.k_proj.weight, self.v_proj.weight),
+                                rope=(cache, S, dh, 2 * H * dh))
+            o = native.attention_core(qkv.view(-1, S, 3, H, dh), cache, rope_done=True)
             return native.linear(o.view(*b, S, d_model), (self.output_proj.weight,))
         q, k, v = self.q_proj(x), self.k_proj(x), self.v_proj(x)
         q, k, v = (t.view(*b, S, H, dh).transpose(-2, -3) for t in (q, k, v))  # (..., H, S, dh)

@@ -69,3 +69,24 @@ def release_all(params=None) -> None:
             s = _slots.get(p)
             if s is not None:
                 s.claimed = False
+
+
+def claim_group(params) -> torch.Tensor | None:
+    """One ``[Σ rows, cols]`` view covering the slots of several 2-D parameters, if they are all unclaimed
+    and lie back to back in the same flat buffer in this order (then ONE wgrad GEMM can produce all of
+    them); otherwise None and nothing is claimed."""
+    slots = [_slots.get(p) for p in params]
+    if any(s is None or s.claimed for s in slots) or any(p.grad is not None for p in params):
+        return None
+    base, off0 = slots[0].base, slots[0].offset
+    cols = params[0].shape[1]
+    off = off0
+    rows = 0
+    for p, s in zip(params, slots):
+        if s.base is not base or s.offset != off or p.dim() != 2 or p.shape[1] != cols:
+            return None
+        off += p.numel()
+        rows += p.shape[0]
+    for s in slots:
+        s.claimed = True
+    return base.narrow(0, off0, rows * cols).view(rows, cols)

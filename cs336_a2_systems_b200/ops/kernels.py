@@ -19,7 +19,7 @@ from .._native import check, p, stream_ptr
 BF16, F32 = 0, 1
 _DT = {torch.bfloat16: BF16, torch.float32: F32}
 
-EPI_BF16, EPI_F32, EPI_F32_ACC, EPI_BF16_SWIGLU, EPI_F32_RESID = 0, 1, 2, 3, 4
+EPI_BF16, EPI_F32, EPI_F32_ACC, EPI_BF16_SWIGLU, EPI_F32_RESID, EPI_BF16_ROPE = 0, 1, 2, 3, 4, 5
 
 #: launch counter (kernels launched through this module), for bench.py's "gpu_launches"
 launches = 0
@@ -48,8 +48,18 @@ def gemm_supported(a: Tensor, b: Tensor) -> bool:
 
 
 def gemm(a: Tensor, b: Tensor, *, a_mn: bool = False, b_mn: bool = False, epilogue: int = EPI_BF16,
-         out: Tensor | None = None, aux: Tensor | None = None, force_bn: int = 0) -> Tensor:
-    """``C = A · Bᵀ``.  ``a``: [M,K] (or [K,M] when ``a_mn``); ``b``: [N,K] (or [K,N] when ``b_mn``)."""
+         out: Tensor | None = None, aux: Tensor | None = None, force_bn: int = 0,
+         rope: tuple | None = None) -> Tensor:
+    """``C = A · Bᵀ``.  ``a``: [M,K] (or [K,M] when ``a_mn``); ``b``: [N,K] (or [K,N] when ``b_mn``).
+
+    ``rope=(cache, S, head_dim, n_cols)`` selects the RoPE epilogue: columns ``< n_cols`` of the bf16 output
+    are rotated (row ``r`` is position ``r % S``)."""
+    rope_S = rope_dh = rope_cols = rope_ctx = 0
+    if rope is not None:
+        cache, rope_S, rope_dh, rope_cols = rope
+        assert cache.dtype == torch.float32 and cache.is_contiguous() and cache.shape[2] * 2 == rope_dh
+        rope_ctx = cache.shape[1]
+        aux, epilogue = cache, EPI_BF16_ROPE
     M, K = (a.shape[1], a.shape[0]) if a_mn else (a.shape[0], a.shape[1])
     N, Kb = (b.shape[1], b.shape[0]) if b_mn else (b.shape[0], b.shape[1])
     if K != Kb:
@@ -58,14 +68,15 @@ def gemm(a: Tensor, b: Tensor, *, a_mn: bool = False, b_mn: bool = False, epilog
         raise ValueError("gemm: operands must be bf16, 2-D, unit inner stride, 16-byte aligned rows")
     n_out = N // 2 if epilogue == EPI_BF16_SWIGLU else N
     if out is None:
-        dt = torch.bfloat16 if epilogue in (EPI_BF16, EPI_BF16_SWIGLU) else torch.float32
+        dt = torch.bfloat16 if epilogue in (EPI_BF16, EPI_BF16_SWIGLU, EPI_BF16_ROPE) else torch.float32
         out = torch.empty(M, n_out, dtype=dt, device=a.device)
     else:
         assert out.shape == (M, n_out) and out.stride(1) == 1
-    ld_aux = aux.stride(0) if aux is not None else 0
-    check(_lib().b200_gemm_bf16(p(a), p(b), p(out), p(aux), c_int(M), c_int(N), c_int(K), c_int(a.stride(0)),
-                                c_int(b.stride(0)), c_int(out.stride(0)), c_int(ld_aux), c_int(int(a_mn)),
-                                c_int(int(b_mn)), c_int(epilogue), c_int(force_bn), stream_ptr()), "gemm")
+    ld_aux = aux.stride(0) if (aux is not None and rope is None) else 0
+    check(_lib().b200_gemm_bf16_ex(p(a), p(b), p(out), p(aux), c_int(M), c_int(N), c_int(K), c_int(a.stride(0)),
+                                   c_int(b.stride(0)), c_int(out.stride(0)), c_int(ld_aux), c_int(int(a_mn)),
+                                   c_int(int(b_mn)), c_int(epilogue), c_int(force_bn), c_int(rope_S), c_int(rope_dh),
+                                   c_int(rope_cols), c_int(rope_ctx), stream_ptr()), "gemm")
     _count()
     return out
 
@@ -313,7 +324,8 @@ def fa2_fwd(q: Tensor, k: Tensor, v: Tensor, causal: bool, out: Tensor | None = 
     return out, lse
 
 
-def fa2_bwd(q, k, v, o, lse, do, causal: bool, dq=None, dk=None, dv=None):
+def fa2_bwd(q, k, v, o, lse, do, causal: bool, dq=None, dk=None, dv=None, rope_cache: Tensor | None = None):
+    """``rope_cache``: when q,k were rotated before attention, un-rotate dq,dk on the way out (fused)."""
     B, H, Nq, D = q.shape
     Nk = k.shape[2]
     if do.stride(3) != 1:
@@ -323,10 +335,15 @@ def fa2_bwd(q, k, v, o, lse, do, causal: bool, dq=None, dk=None, dv=None):
     dv = torch.empty_like(v) if dv is None else dv
     delta = torch.empty(B, H, Nq, dtype=torch.float32, device=q.device)
     dq_acc = torch.empty(B, H, Nq, D, dtype=torch.float32, device=q.device)
-    check(_lib().b200_fa2_bwd(p(q), p(k), p(v), p(o), p(lse), p(do), p(dq), p(dk), p(dv), p(delta), p(dq_acc),
-                              c_int(B), c_int(H), c_int(Nq), c_int(Nk), c_int(D), _strides3(q), _strides3(k),
-                              _strides3(v), _strides3(o), _strides3(do), _strides3(dq), _strides3(dk), _strides3(dv),
-                              c_int(int(causal)), c_float(1.0 / (D ** 0.5)), stream_ptr()), "fa2_bwd")
+    rope_ctx = 0
+    if rope_cache is not None:
+        assert rope_cache.dtype == torch.float32 and rope_cache.is_contiguous() and rope_cache.shape[2] * 2 == D
+        rope_ctx = rope_cache.shape[1]
+    check(_lib().b200_fa2_bwd_rope(p(q), p(k), p(v), p(o), p(lse), p(do), p(dq), p(dk), p(dv), p(delta), p(dq_acc),
+                                   c_int(B), c_int(H), c_int(Nq), c_int(Nk), c_int(D), _strides3(q), _strides3(k),
+                                   _strides3(v), _strides3(o), _strides3(do), _strides3(dq), _strides3(dk),
+                                   _strides3(dv), c_int(int(causal)), c_float(1.0 / (D ** 0.5)), p(rope_cache),
+                                   c_int(rope_ctx), stream_ptr()), "fa2_bwd")
     _count(4)
     return dq, dk, dv
 

@@ -125,13 +125,16 @@ def _to_bf16_2d(x: Tensor, K: int) -> Tensor:
 
 
 class LinearFn(torch.autograd.Function):
-    """``y = x · [W_0; W_1; …]ᵀ`` on the tcgen05 GEMM; backward = dgrad (NN) + one wgrad (TN) per weight."""
+    """``y = x · [W_0; W_1; …]ᵀ`` on the tcgen05 GEMM; backward = dgrad (NN) + wgrad (TN).
+
+    The wgrad of a fused group is ONE GEMM when the members' gradient slots are adjacent (flat arena in
+    parameter order), else one per weight.  ``rope`` fuses RoPE into the forward epilogue."""
 
     @staticmethod
-    def forward(ctx, x: Tensor, wb: Tensor, *weights: Tensor):
+    def forward(ctx, x: Tensor, wb: Tensor, rope, *weights: Tensor):
         N, K = wb.shape
         x2 = _to_bf16_2d(x, K)
-        y = kernels.gemm(x2, wb)
+        y = kernels.gemm(x2, wb, rope=rope)
         ctx.save_for_backward(x2, wb)
         ctx.weights = weights
         ctx.x_shape = x.shape
@@ -149,11 +152,22 @@ class LinearFn(torch.autograd.Function):
             dx = dx.view(ctx.x_shape)
             if ctx.x_dtype != BF16:
                 dx = dx.to(ctx.x_dtype)
+        ws = ctx.weights
+        need = ctx.needs_input_grad[3:]
+        if len(ws) > 1 and all(need):
+            joint = grad_slots.claim_group(ws)
+            if joint is not None:
+                kernels.gemm(dy2, x2, a_mn=True, b_mn=True, epilogue=kernels.EPI_F32, out=joint)
+                dws, r0 = [], 0
+                for w in ws:
+                    dws.append(joint[r0:r0 + w.shape[0]])
+                    r0 += w.shape[0]
+                return (dx, None, None, *dws)
         dws = []
         r0 = 0
-        for i, w in enumerate(ctx.weights):
+        for i, w in enumerate(ws):
             n_i = w.shape[0]
-            if ctx.needs_input_grad[2 + i]:
+            if need[i]:
                 dst = grad_slots.claim(w)
                 dyi = dy2[:, r0:r0 + n_i]  # column slice: MN-major A operand with lda = N
                 if dyi.data_ptr() % 16 != 0:
@@ -162,13 +176,14 @@ class LinearFn(torch.autograd.Function):
             else:
                 dws.append(None)
             r0 += n_i
-        return (dx, None, *dws)
+        return (dx, None, None, *dws)
 
 
-def linear(x: Tensor, weights: tuple[Tensor, ...]) -> Tensor:
-    """Apply one or several bias-free linear maps that share the input (outputs concatenated)."""
+def linear(x: Tensor, weights: tuple[Tensor, ...], rope: tuple | None = None) -> Tensor:
+    """Apply one or several bias-free linear maps that share the input (outputs concatenated).
+    ``rope=(cache, S, head_dim, n_cols)`` rotates the first ``n_cols`` output columns (fused QKV → q,k)."""
     wb = weight_shadow(weights)
-    return LinearFn.apply(x, wb, *weights)
+    return LinearFn.apply(x, wb, rope, *weights)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -250,10 +265,11 @@ class AttentionCoreFn(torch.autograd.Function):
     buffer and un-rotates dq,dk in place — ready to be the dgrad/wgrad GEMM operand."""
 
     @staticmethod
-    def forward(ctx, qkv: Tensor, rope_cache: Tensor):
+    def forward(ctx, qkv: Tensor, rope_cache: Tensor, rope_done: bool = False):
         B, S, _, H, dh = qkv.shape
         assert qkv.is_contiguous()
-        kernels.rope_qk_inplace(qkv, rope_cache)
+        if not rope_done:  # otherwise the QKV GEMM epilogue already rotated q and k
+            kernels.rope_qk_inplace(qkv, rope_cache)
         q, k, v = (qkv[:, :, i].permute(0, 2, 1, 3) for i in range(3))  # (B, H, S, dh) strided views
         o = torch.empty(B, S, H, dh, dtype=BF16, device=qkv.device)
         _, lse = kernels.fa2_fwd(q, k, v, True, out=o.permute(0, 2, 1, 3))
@@ -268,13 +284,13 @@ class AttentionCoreFn(torch.autograd.Function):
         dqkv = torch.empty_like(qkv)
         dq, dk, dv = (dqkv[:, :, i].permute(0, 2, 1, 3) for i in range(3))
         do4 = do.contiguous().view(B, S, H, dh).permute(0, 2, 1, 3)
-        kernels.fa2_bwd(q, k, v, o.permute(0, 2, 1, 3), lse, do4, True, dq=dq, dk=dk, dv=dv)
-        kernels.rope_qk_inplace(dqkv, rope_cache, inverse=True)
-        return dqkv, None
+        # dq, dk are un-rotated inside the backward kernels (dq in its fp32→bf16 pass, dk in the epilogue)
+        kernels.fa2_bwd(q, k, v, o.permute(0, 2, 1, 3), lse, do4, True, dq=dq, dk=dk, dv=dv, rope_cache=rope_cache)
+        return dqkv, None, None
 
 
-def attention_core(qkv: Tensor, rope_cache: Tensor) -> Tensor:
-    return AttentionCoreFn.apply(qkv, rope_cache)
+def attention_core(qkv: Tensor, rope_cache: Tensor, rope_done: bool = False) -> Tensor:
+    return AttentionCoreFn.apply(qkv, rope_cache, rope_done)
 
 
 # ------------------------------------------------------------------------------------------------

@@ -188,7 +188,9 @@ class DDPBucketed(_DDPBase):
         for idxs in plan_buckets(order, bucket_size_mb):
             b = _Bucket(order[idxs[0]].dtype, order[idxs[0]].device)
             align = max(1, self.ALIGN_BYTES // order[idxs[0]].element_size())
-            for i in idxs:
+            # membership follows the (reversed) readiness order, but inside a bucket the slots are laid out in
+            # forward parameter order so that q/k/v gradients are adjacent (one wgrad GEMM writes all three)
+            for i in sorted(idxs, reverse=True):
                 p = order[i]
                 b.params.append(p)
                 b.offsets.append(b.numel)

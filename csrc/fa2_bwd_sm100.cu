@@ -51,6 +51,8 @@ struct BwdParams {
   int causal;
   float scale, scale_log2;
   int num_q_tiles;
+  const float* rope_cache;  // nullable: (2, rope_ctx, D/2) cos/sin (used by the dq/dk post-passes)
+  int rope_ctx;
 };
 
 __device__ __forceinline__ uint32_t swz_off_b(int row, int col, int rows) {
@@ -357,7 +359,8 @@ __global__ void fa2_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv
 }
 
 __global__ void fa2_dq_convert_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dq, int H, int Nq,
-                                      int D, long long sb, long long sh, long long sr, long long total) {
+                                      int D, long long sb, long long sh, long long sr, long long total,
+                                      const float* __restrict__ rope_cache, int rope_ctx) {
   const long long idx = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 2;
   if (idx >= total) return;
   const int d = (int)(idx % D);
@@ -366,8 +369,34 @@ __global__ void fa2_dq_convert_kernel(const float* __restrict__ acc, __nv_bfloat
   const long long bh = rowi / Nq;
   const int hh = (int)(bh % H);
   const long long bb = bh / H;
-  const float2 v = *reinterpret_cast<const float2*>(acc + idx);
+  float2 v = *reinterpret_cast<const float2*>(acc + idx);
+  if (rope_cache != nullptr) {  // un-rotate the pair (d, d+1) by the angle of position i
+    const int half = D >> 1;
+    const float cs = rope_cache[(size_t)i * half + (d >> 1)];
+    const float sn = rope_cache[(size_t)rope_ctx * half + (size_t)i * half + (d >> 1)];
+    v = make_float2(cs * v.x + sn * v.y, cs * v.y - sn * v.x);
+  }
   *reinterpret_cast<uint32_t*>(dq + bb * sb + hh * sh + (long long)i * sr + d) = pack_bf16x2(v.x, v.y);
+}
+
+// dK was computed w.r.t. the rotated keys: rotate every (2i, 2i+1) pair back by -angle(position = key index), in place
+__global__ void fa2_dk_unrope_kernel(__nv_bfloat16* __restrict__ dk, int H, int Nk, int D, long long sb, long long sh,
+                                     long long sr, long long total_pairs, const float* __restrict__ rope_cache,
+                                     int rope_ctx) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total_pairs) return;
+  const int half = D >> 1;
+  const int pi = (int)(idx % half);
+  const long long rowi = idx / half;
+  const int i = (int)(rowi % Nk);
+  const long long bh = rowi / Nk;
+  const int hh = (int)(bh % H);
+  const long long bb = bh / H;
+  uint32_t* ptr = reinterpret_cast<uint32_t*>(dk + bb * sb + hh * sh + (long long)i * sr + 2 * pi);
+  const float2 v = unpack_bf16x2(*ptr);
+  const float cs = rope_cache[(size_t)i * half + pi];
+  const float sn = rope_cache[(size_t)rope_ctx * half + (size_t)i * half + pi];
+  *ptr = pack_bf16x2(cs * v.x + sn * v.y, cs * v.y - sn * v.x);
 }
 
 template <int DP>
@@ -389,15 +418,34 @@ static int launch_bwd(const CUtensorMap& q, const CUtensorMap& k, const CUtensor
 }  // namespace fa2
 }  // namespace b200
 
+extern "C" int b200_fa2_bwd_rope(const void* q, const void* k, const void* v, const void* o, const float* lse,
+                                 const void* dout, void* dq, void* dk, void* dv, float* delta, float* dq_acc, int B,
+                                 int H, int Nq, int Nk, int D, const long long* q_strides, const long long* k_strides,
+                                 const long long* v_strides, const long long* o_strides, const long long* do_strides,
+                                 const long long* dq_strides, const long long* dk_strides, const long long* dv_strides,
+                                 int causal, float scale, const float* rope_cache, int rope_ctx, void* stream);
+
 extern "C" int b200_fa2_bwd(const void* q, const void* k, const void* v, const void* o, const float* lse,
                             const void* dout, void* dq, void* dk, void* dv, float* delta, float* dq_acc, int B, int H,
                             int Nq, int Nk, int D, const long long* q_strides, const long long* k_strides,
                             const long long* v_strides, const long long* o_strides, const long long* do_strides,
                             const long long* dq_strides, const long long* dk_strides, const long long* dv_strides,
                             int causal, float scale, void* stream) {
+  return b200_fa2_bwd_rope(q, k, v, o, lse, dout, dq, dk, dv, delta, dq_acc, B, H, Nq, Nk, D, q_strides, k_strides,
+                           v_strides, o_strides, do_strides, dq_strides, dk_strides, dv_strides, causal, scale, nullptr,
+                           0, stream);
+}
+
+extern "C" int b200_fa2_bwd_rope(const void* q, const void* k, const void* v, const void* o, const float* lse,
+                            const void* dout, void* dq, void* dk, void* dv, float* delta, float* dq_acc, int B, int H,
+                            int Nq, int Nk, int D, const long long* q_strides, const long long* k_strides,
+                            const long long* v_strides, const long long* o_strides, const long long* do_strides,
+                            const long long* dq_strides, const long long* dk_strides, const long long* dv_strides,
+                            int causal, float scale, const float* rope_cache, int rope_ctx, void* stream) {
   using namespace b200;
   using namespace b200::fa2;
   B200_REQUIRE(B > 0 && H > 0 && Nq > 0 && Nk > 0, "fa2_bwd: empty problem");
+  B200_REQUIRE(rope_cache == nullptr || (Nq <= rope_ctx && Nk <= rope_ctx), "fa2_bwd: sequence exceeds the RoPE cache");
   B200_REQUIRE(D >= 8 && D <= 128 && D % 8 == 0, "fa2_bwd: head dim %d unsupported (multiple of 8, <= 128)", D);
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const long long rows = (long long)B * H * Nq;
@@ -424,14 +472,23 @@ extern "C" int b200_fa2_bwd(const void* q, const void* k, const void* v, const v
   p.H = H; p.Nq = Nq; p.Nk = Nk; p.D = D; p.causal = causal;
   p.scale = scale; p.scale_log2 = scale * kLog2e;
   p.num_q_tiles = ceil_div(Nq, BM);
+  p.rope_cache = rope_cache; p.rope_ctx = rope_ctx;
   rc = D <= 64 ? launch_bwd<64>(tq, tk, tv, tdo, p, B, s) : launch_bwd<128>(tq, tk, tv, tdo, p, B, s);
   if (rc) return rc;
   {
     const long long total = rows * D;
     const int threads = 256;
     fa2_dq_convert_kernel<<<(unsigned)((total / 2 + threads - 1) / threads), threads, 0, s>>>(
-        dq_acc, reinterpret_cast<__nv_bfloat16*>(dq), H, Nq, D, dq_strides[0], dq_strides[1], dq_strides[2], total);
+        dq_acc, reinterpret_cast<__nv_bfloat16*>(dq), H, Nq, D, dq_strides[0], dq_strides[1], dq_strides[2], total,
+        rope_cache, rope_ctx);
     B200_LAUNCH_CHECK();
+    if (rope_cache != nullptr) {
+      const long long pairs = (long long)B * H * Nk * (D / 2);
+      fa2_dk_unrope_kernel<<<(unsigned)((pairs + threads - 1) / threads), threads, 0, s>>>(
+          reinterpret_cast<__nv_bfloat16*>(dk), H, Nk, D, dk_strides[0], dk_strides[1], dk_strides[2], pairs,
+          rope_cache, rope_ctx);
+      B200_LAUNCH_CHECK();
+    }
   }
   return 0;
 }

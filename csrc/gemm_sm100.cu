@@ -36,6 +36,9 @@ enum Epilogue : int {
   EPI_F32_ACC = 2,   // C fp32 += acc
   EPI_BF16_SWIGLU = 3,  // C bf16 [M, N/2] = silu(acc[:, 2j]) * acc[:, 2j+1]   (interleaved gate/up columns)
   EPI_F32_RESID = 4,    // C fp32 = aux fp32 + acc   (residual add)
+  EPI_BF16_ROPE = 5,    // C bf16 = acc with RoPE applied to columns < rope_cols (fused QKV projection):
+                        //   row r is token position r % rope_S, column c is element c % rope_dh of its head,
+                        //   aux = fp32 cos/sin cache (2, rope_ctx, rope_dh/2)
 };
 
 struct Params {
@@ -44,6 +47,7 @@ struct Params {
   int M, N, K;
   int ldc, ld_aux;
   int num_m, num_n, num_k;
+  int rope_S, rope_dh, rope_cols, rope_ctx;
 };
 
 template <int BN>
@@ -61,7 +65,45 @@ __device__ __forceinline__ void store_chunk(const Params& p, int row, int col0, 
   // one thread owns one output row; r[] holds 32 consecutive fp32 accumulator columns
   if (row >= p.M || col0 >= p.N) return;
   const bool full = (col0 + 32 <= p.N);
-  if constexpr (EPI == EPI_BF16) {
+  if constexpr (EPI == EPI_BF16_ROPE) {
+    __nv_bfloat16* c = reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + col0;
+    float v[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+    if (col0 < p.rope_cols) {
+      const float* cache = reinterpret_cast<const float*>(p.aux);
+      const int half = p.rope_dh >> 1;
+      const int pos = row % p.rope_S;
+      const float* cosr = cache + (size_t)pos * half;
+      const float* sinr = cache + (size_t)p.rope_ctx * half + (size_t)pos * half;
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int col = col0 + 2 * j;
+        if (col < p.rope_cols) {
+          const int i = (col % p.rope_dh) >> 1;
+          const float cs = cosr[i], sn = sinr[i];
+          const float a = v[2 * j], b = v[2 * j + 1];
+          v[2 * j] = cs * a - sn * b;
+          v[2 * j + 1] = sn * a + cs * b;
+        }
+      }
+    }
+    if (full && (p.ldc & 7) == 0) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        u32x4 o;
+        o.x = pack_bf16x2(v[8 * q + 0], v[8 * q + 1]);
+        o.y = pack_bf16x2(v[8 * q + 2], v[8 * q + 3]);
+        o.z = pack_bf16x2(v[8 * q + 4], v[8 * q + 5]);
+        o.w = pack_bf16x2(v[8 * q + 6], v[8 * q + 7]);
+        *reinterpret_cast<u32x4*>(c + 8 * q) = o;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j < p.N) c[j] = __float2bfloat16(v[j]);
+    }
+  } else if constexpr (EPI == EPI_BF16) {
     __nv_bfloat16* c = reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + col0;
     if (full && (p.ldc & 7) == 0) {
 #pragma unroll
@@ -324,6 +366,9 @@ static int dispatch_epi(int epi, const CUtensorMap& a, const CUtensorMap& b, con
     case EPI_F32_RESID:
       if constexpr (!A_MN && !B_MN) return launch<BN, A_MN, B_MN, EPI_F32_RESID>(a, b, p, s);
       break;
+    case EPI_BF16_ROPE:
+      if constexpr (!A_MN && !B_MN) return launch<BN, A_MN, B_MN, EPI_BF16_ROPE>(a, b, p, s);
+      break;
   }
   set_error("gemm: unsupported epilogue %d for this operand layout", epi);
   return B200_ERR_ARG;
@@ -341,9 +386,20 @@ static int dispatch_major(bool a_mn, bool b_mn, int epi, const CUtensorMap& a, c
 }  // namespace gemm
 }  // namespace b200
 
+extern "C" int b200_gemm_bf16_ex(const void* A, const void* B, void* C, const void* aux, int M, int N, int K, int lda,
+                                 int ldb, int ldc, int ld_aux, int a_mn_major, int b_mn_major, int epilogue,
+                                 int force_bn, int rope_S, int rope_dh, int rope_cols, int rope_ctx, void* stream);
+
 extern "C" int b200_gemm_bf16(const void* A, const void* B, void* C, const void* aux, int M, int N, int K, int lda,
                               int ldb, int ldc, int ld_aux, int a_mn_major, int b_mn_major, int epilogue,
                               int force_bn, void* stream) {
+  return b200_gemm_bf16_ex(A, B, C, aux, M, N, K, lda, ldb, ldc, ld_aux, a_mn_major, b_mn_major, epilogue, force_bn,
+                           0, 0, 0, 0, stream);
+}
+
+extern "C" int b200_gemm_bf16_ex(const void* A, const void* B, void* C, const void* aux, int M, int N, int K, int lda,
+                                 int ldb, int ldc, int ld_aux, int a_mn_major, int b_mn_major, int epilogue,
+                                 int force_bn, int rope_S, int rope_dh, int rope_cols, int rope_ctx, void* stream) {
   using namespace b200;
   using namespace b200::gemm;
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
@@ -370,6 +426,10 @@ extern "C" int b200_gemm_bf16(const void* A, const void* B, void* C, const void*
   Params p;
   p.C = C; p.aux = aux; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.ld_aux = ld_aux;
   p.num_m = ceil_div(M, BM); p.num_n = ceil_div(N, bn); p.num_k = ceil_div(K, BK);
+  p.rope_S = rope_S; p.rope_dh = rope_dh; p.rope_cols = rope_cols; p.rope_ctx = rope_ctx;
+  if (epilogue == EPI_BF16_ROPE)
+    B200_REQUIRE(aux && rope_S > 0 && rope_dh > 0 && (rope_dh % 2) == 0 && rope_S <= rope_ctx && (rope_cols % 2) == 0,
+                 "gemm: RoPE epilogue needs the cos/sin cache, S <= ctx and an even head dim");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   switch (bn) {
     case 256: return dispatch_major<256>(a_mn, b_mn, epilogue, tmA, tmB, p, s);

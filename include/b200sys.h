@@ -32,6 +32,12 @@ int b200_device_info(int* sm_count, int* cc_major, int* cc_minor);
  * ref: every Linear of the LM → cuBLAS (cs336-basics/cs336_basics/model.py:41). */
 int b200_gemm_bf16(const void* A, const void* B, void* C, const void* aux, int M, int N, int K, int lda, int ldb,
                    int ldc, int ld_aux, int a_mn_major, int b_mn_major, int epilogue, int force_bn, void* stream);
+/* Same, plus epilogue 5: C bf16 = acc with RoPE (interleaved pairs, ref model.py:135-147) applied to columns
+ * < rope_cols — the fused QKV projection writes rotated q,k directly.  Row r is position r % rope_S, column c is
+ * element c % rope_dh of its head; aux = fp32 cos/sin cache (2, rope_ctx, rope_dh/2). */
+int b200_gemm_bf16_ex(const void* A, const void* B, void* C, const void* aux, int M, int N, int K, int lda, int ldb,
+                      int ldc, int ld_aux, int a_mn_major, int b_mn_major, int epilogue, int force_bn, int rope_S,
+                      int rope_dh, int rope_cols, int rope_ctx, void* stream);
 
 /* ---- FlashAttention-2 (tcgen05/TMEM/TMA) ------------------------------------------------------
  * q,k,v,o: bf16 with element strides (batch, head, row); last dim contiguous, D in {16,32,64,80,96,128}.

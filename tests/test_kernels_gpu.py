@@ -86,8 +86,34 @@ def test_gemm_residual_and_swiglu_epilogues():
     assert out.shape == (256, 192) and _rel_err(out, ref) < 1e-2
 
 
+def test_gemm_rope_epilogue_and_fused_inverse_in_fa_bwd():
+    """QKV GEMM with RoPE fused in the epilogue == GEMM then rope kernel; FA backward un-rotates dq/dk."""
+    k = _k()
+    torch.manual_seed(3)
+    B, S, H, dh = 2, 128, 3, 64
+    d = H * dh
+    cache = F_ref.rope_cache(256, dh, device="cuda")
+    x = _bf(torch.randn(B * S, d, device="cuda"))
+    w = _bf(torch.randn(3 * d, d, device="cuda") * 0.05)
+    fused = k.gemm(x, w, rope=(cache, S, dh, 2 * d)).view(B, S, 3, H, dh)
+    plain = k.gemm(x, w).view(B, S, 3, H, dh).clone()
+    k.rope_qk_inplace(plain, cache)
+    assert _rel_err(fused, plain) < 6e-3
+    assert torch.equal(fused[:, :, 2], plain[:, :, 2])
+    # backward: fused un-rotation vs explicit inverse-rope kernel
+    q, kk, v = (fused[:, :, i].permute(0, 2, 1, 3) for i in range(3))
+    o, lse = k.fa2_fwd(q, kk, v, True)
+    do = _bf(torch.randn(B, H, S, dh, device="cuda"))
+    a = torch.empty(B, S, 3, H, dh, dtype=torch.bfloat16, device="cuda")
+    b = torch.empty_like(a)
+    k.fa2_bwd(q, kk, v, o, lse, do, True, *(a[:, :, i].permute(0, 2, 1, 3) for i in range(3)), rope_cache=cache)
+    k.fa2_bwd(q, kk, v, o, lse, do, True, *(b[:, :, i].permute(0, 2, 1, 3) for i in range(3)))
+    k.rope_qk_inplace(b, cache, inverse=True)
+    assert _rel_err(a, b) < 1e-2
+
+
 # ------------------------------------------------------------------------------------------------ norms
-@pytest.mark.parametrize("T,d", [(64, 768), (2048, 1600), (33, 2560), (7, 100)])
+@pytest.mark.parametrize("T,d", [(64, 768), (2048, 1600), (33, 2560), (7, 100), (300, 3072), (16, 4096)])
 def test_rmsnorm_fwd_bwd(T, d):
     k = _k()
     torch.manual_seed(0)
