@@ -43,6 +43,8 @@ def parse_args():
     ap.add_argument("--bucket-mb", type=float, default=100.0)
     ap.add_argument("--no-graph", action="store_true", help="ours: do not capture the step in a CUDA graph")
     ap.add_argument("--comm", default=None, help="ours: gradient backend override (symm | c10d)")
+    ap.add_argument("--no-overlap", action="store_true",
+                    help="ours: run the optimizer after backward instead of overlapping it with backward")
     return ap.parse_args()
 
 
@@ -114,7 +116,8 @@ def build_ours(args, rank, ws, dev):
     if ws > 1:
         model = DDPBucketed(model, bucket_size_mb=args.bucket_mb, backend=args.comm)
     opt = AdamW(model.parameters(), lr=1e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
-    trainer = Trainer(model, opt, autocast=True, cuda_graph=not args.no_graph)
+    trainer = Trainer(model, opt, autocast=True, cuda_graph=not args.no_graph,
+                      overlap_optimizer=not args.no_overlap)
     state = {"launches_per_step": 0}
 
     def step_device(x, y):
@@ -128,7 +131,7 @@ def build_ours(args, rank, ws, dev):
         trainer._step_eager(x, y)
         state["launches_per_step"] = kernels.launches - n0
 
-    extra = {"cuda_graph": not args.no_graph,
+    extra = {"cuda_graph": not args.no_graph, "optimizer_overlapped_with_backward": not args.no_overlap,
              "comm": getattr(getattr(model, "_reducer", None), "kind", "none")}
     return step_device, step_e2e, count_launches, state, extra
 

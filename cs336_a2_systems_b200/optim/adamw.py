@@ -47,7 +47,8 @@ class AdamW(torch.optim.Optimizer):
             raise ValueError(f"Invalid beta parameter at index 1: {betas[1]}")
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
         self._fused = fused
-        self._plans: dict[int, object] = {}
+        self._plans: dict[object, object] = {}
+        self._done: set[int] = set()  # ids of params already stepped this iteration by step_subset()
 
     # ------------------------------------------------------------------ reference arithmetic
     @staticmethod
@@ -85,7 +86,7 @@ class AdamW(torch.optim.Optimizer):
             lr, (b1, b2), eps, wd = group["lr"], group["betas"], group["eps"], group["weight_decay"]
             fused_ps = []
             for p in group["params"]:
-                if p.grad is None:
+                if p.grad is None or id(p) in self._done:
                     continue
                 if self._fusable(p):
                     fused_ps.append(p)
@@ -93,7 +94,33 @@ class AdamW(torch.optim.Optimizer):
                     self._step_param_torch(p, self.state[p], lr, b1, b2, eps, wd)
             if fused_ps:
                 self._step_fused(gi, fused_ps, lr, b1, b2, eps, wd)
+        self._done.clear()
         return loss
+
+    @torch.no_grad()
+    def step_subset(self, key, params) -> None:
+        """Update only ``params`` now (one fused launch on the current stream); the next :meth:`step`
+        skips them.  This is what lets a trainer run the optimizer for a layer on a side stream as soon
+        as that layer's gradients are final, overlapped with the rest of backward ("optimizer in
+        backward"); the arithmetic is exactly that of :meth:`step`."""
+        group_of = getattr(self, "_group_of", None)
+        if group_of is None:
+            group_of = {id(p): gi for gi, g in enumerate(self.param_groups) for p in g["params"]}
+            self._group_of = group_of
+        by_group: dict[int, list] = {}
+        for p in params:
+            if p.grad is not None and id(p) not in self._done:
+                by_group.setdefault(group_of[id(p)], []).append(p)
+        for gi, ps in by_group.items():
+            g = self.param_groups[gi]
+            lr, (b1, b2), eps, wd = g["lr"], g["betas"], g["eps"], g["weight_decay"]
+            fus = [p for p in ps if self._fusable(p)]
+            for p in ps:
+                if not self._fusable(p):
+                    self._step_param_torch(p, self.state[p], lr, b1, b2, eps, wd)
+            if fus:
+                self._step_fused((gi, key), fus, lr, b1, b2, eps, wd)
+            self._done.update(id(p) for p in ps)
 
     # ------------------------------------------------------------------ fused sm_100a path
     def _step_fused(self, gi: int, ps, lr, b1, b2, eps, wd):
@@ -124,7 +151,7 @@ class AdamW(torch.optim.Optimizer):
 
     def sync_step_from_device(self) -> None:
         """After CUDA-graph replays the host ``t`` mirrors are stale; refresh them from the device."""
-        for gi, plan in self._plans.items():
+        for _key, plan in self._plans.items():
             t = plan.device_step()
             for p in plan.params:
                 self.state[p]["t"] = t

@@ -39,13 +39,27 @@ class C10dReducer:
     def _reduce(self, t: torch.Tensor):
         op = dist.ReduceOp.AVG if (self._avg and t.is_cuda) else dist.ReduceOp.SUM
         work = dist.all_reduce(t, op=op, group=self.group, async_op=True)
-        return (work, t, op != dist.ReduceOp.SUM)
+        return [work, t, op != dist.ReduceOp.SUM]  # mutable: stream_after() may apply the average early
 
     def reduce_bucket_async(self, bi: int):
         return self._reduce(self._bufs[bi])
 
     def reduce_param_async(self, idx: int, param: torch.Tensor):
         return self._reduce(param.grad)
+
+    def stream_after(self, handle):
+        """A side stream that has been made to wait for this reduction (and applies the gloo-style average)."""
+        work, t, averaged = handle
+        if not t.is_cuda:
+            raise RuntimeError("bucket callbacks need CUDA tensors")
+        if getattr(self, "_side", None) is None:
+            self._side = torch.cuda.Stream(device=t.device)
+        with torch.cuda.stream(self._side):
+            work.wait()
+            if not averaged:
+                t.div_(self.world_size)
+                handle[2] = True
+        return self._side
 
     def wait(self, handles) -> None:
         for work, _t, _ in handles:

@@ -199,6 +199,7 @@ class DDPBucketed(_DDPBase):
             self.buckets.append(b)
         self._reducer = None
         self._pending: list = []
+        self._bucket_callback = None
         if self.world_size > 1:
             self._reducer = _comm.make_reducer([b.numel for b in self.buckets], self.process_group, backend,
                                                per_parameter=False,
@@ -240,7 +241,16 @@ class DDPBucketed(_DDPBase):
         b = self.buckets[bi]
         b.launched = True
         with nvtx.range(f"ddp.allreduce_bucket{bi}"):
-            self._pending.append(self._reducer.reduce_bucket_async(bi))
+            handle = self._reducer.reduce_bucket_async(bi)
+            self._pending.append(handle)
+        if self._bucket_callback is not None:
+            # chain work behind this bucket's reduction (e.g. the optimizer update of exactly these parameters)
+            self._bucket_callback(bi, b.params, self._reducer.stream_after(handle))
+
+    def set_bucket_callback(self, fn) -> None:
+        """``fn(bucket_index, params, stream)`` is called right after a bucket's reduction has been enqueued;
+        ``stream`` is a CUDA stream on which the reduced gradients are valid once its prior work completes."""
+        self._bucket_callback = fn
 
     def finish_gradient_synchronization(self) -> None:
         if self._reducer is not None:

@@ -148,6 +148,9 @@ class SymmReducer:
             param.grad = buf.view_as(g)
         return self._launch(idx)
 
+    def stream_after(self, handle):
+        return self.stream  # reductions are stream-ordered on the reducer's own stream
+
     def wait(self, handles) -> None:
         if not handles:
             return

@@ -46,9 +46,70 @@ class GradArena:
         grad_slots.release_all(self.params)
 
 
+class _OptimizerOverlap:
+    """Runs the fused AdamW for a group of parameters on a side stream as soon as their gradients are
+    final, while backward continues (memory-bound optimizer under compute-bound GEMMs).
+
+    Single process: parameters are grouped into units of ~``unit_mb`` in reverse order and a
+    post-accumulate-grad hook launches a unit when its last gradient has been produced.  Under DDP the
+    unit is a gradient bucket and the launch is chained behind that bucket's all-reduce.
+    Requires every parameter to receive exactly one gradient per step (true for the LM)."""
+
+    def __init__(self, model, optimizer, device, unit_mb: float, is_ddp: bool):
+        self.optimizer = optimizer
+        self.device = device
+        self.stream = torch.cuda.Stream(device=device)
+        self._used = False
+        if is_ddp and hasattr(model, "set_bucket_callback"):
+            model.set_bucket_callback(self._on_bucket)
+            self.units = None
+            return
+        params = [p for p in model.parameters() if p.requires_grad]
+        cap = unit_mb * 1024 * 1024
+        self.units: list[list] = []
+        cur, cur_b = [], 0
+        for p in reversed(params):
+            cur.append(p)
+            cur_b += p.numel() * p.element_size()
+            if cur_b >= cap:
+                self.units.append(cur)
+                cur, cur_b = [], 0
+        if cur:
+            self.units.append(cur)
+        self._count = [0] * len(self.units)
+        for ui, unit in enumerate(self.units):
+            for p in unit:
+                p.register_post_accumulate_grad_hook(self._make_hook(ui))
+
+    def _make_hook(self, ui: int):
+        def hook(param):
+            self._count[ui] += 1
+            if self._count[ui] == len(self.units[ui]):
+                self._count[ui] = 0
+                self._launch(ui, self.units[ui], torch.cuda.current_stream(self.device))
+        return hook
+
+    def _launch(self, key, params, after_stream) -> None:
+        ev = torch.cuda.Event()
+        ev.record(after_stream)
+        self.stream.wait_event(ev)
+        with torch.cuda.stream(self.stream):
+            self.optimizer.step_subset(key, params)
+        self._used = True
+
+    def _on_bucket(self, bucket_index: int, params, reduce_stream) -> None:
+        self._launch(("bucket", bucket_index), params, reduce_stream)
+
+    def join(self) -> None:
+        if self._used:
+            torch.cuda.current_stream(self.device).wait_stream(self.stream)
+            self._used = False
+
+
 class Trainer:
     def __init__(self, model: torch.nn.Module, optimizer: torch.optim.Optimizer, *, autocast: bool = True,
-                 max_grad_norm: float | None = None, cuda_graph: bool = False, grad_arena: bool | None = None):
+                 max_grad_norm: float | None = None, cuda_graph: bool = False, grad_arena: bool | None = None,
+                 overlap_optimizer: bool = False, overlap_unit_mb: float = 128.0):
         self.model = model
         self.optimizer = optimizer
         self.autocast = autocast
@@ -59,6 +120,10 @@ class Trainer:
         self.arena = None
         if grad_arena or (grad_arena is None and self.device.type == "cuda" and not self._is_ddp):
             self.arena = GradArena(list(model.parameters()))
+        self._overlap = None
+        if overlap_optimizer and self.device.type == "cuda" and max_grad_norm is None and \
+                hasattr(optimizer, "step_subset"):
+            self._overlap = _OptimizerOverlap(model, optimizer, self.device, overlap_unit_mb, self._is_ddp)
         self._graph = None
         self._static_x = self._static_y = self._static_loss = None
         self._warm_steps = 0
@@ -84,6 +149,8 @@ class Trainer:
         if self._is_ddp:
             with nvtx.range("grad_sync"):
                 self.model.finish_gradient_synchronization()
+        if self._overlap is not None:
+            self._overlap.join()
         if self.max_grad_norm is not None:
             clip_gradient(self.model.parameters(), self.max_grad_norm)
         with nvtx.range("optimizer"):

@@ -128,49 +128,59 @@ __global__ void __launch_bounds__(256) rmsnorm_bwd_kernel(const TDY* __restrict_
 //      front), warp-shuffle dot product, no block barrier;
 //  (2) dw: column-parallel partial sums over chunks of rows (each thread owns 4 columns, coalesced),
 //      re-reading dy and x (+20 MB at XL, ≈3 µs) — cheaper than starving (1) of registers.
-template <typename TDY, int VPL>
+template <typename TDY>
+__device__ __forceinline__ f32x4 ld_dy4(const TDY* dy, size_t off) {
+  if constexpr (sizeof(TDY) == 2) {
+    const uint2 raw = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(dy) + off);
+    const float2 a = unpack_bf16x2(raw.x), b = unpack_bf16x2(raw.y);
+    return f32x4{a.x, a.y, b.x, b.y};
+  } else {
+    return *reinterpret_cast<const f32x4*>(reinterpret_cast<const float*>(dy) + off);
+  }
+}
+
+// dx: one 128-thread CTA per row, the row's g = dy*w and x held in registers (<= VPT float4 per thread, all
+// loads issued up front), one block reduction.  T rows -> T CTAs: enough bytes in flight to run at HBM speed
+// even for T = 2048 (a warp-per-row variant had too few loads outstanding per SM).
+template <typename TDY, int VPT>
 __global__ void __launch_bounds__(128) rmsnorm_bwd_dx_kernel(const TDY* __restrict__ dy, const float* __restrict__ x,
                                                              const float* __restrict__ w, const float* __restrict__ rstd,
                                                              const float* __restrict__ dres_in, float* __restrict__ dx,
                                                              __nv_bfloat16* __restrict__ dx_bf16, int T, int d) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int r = blockIdx.x * 4 + warp;
-  if (r >= T) return;
+  __shared__ float red[32];
+  const int r = blockIdx.x;
   const int nvec = d >> 2;
   const size_t base = (size_t)r * d;
   const float rs = rstd[r];
-  f32x4 g[VPL], xh[VPL];
-  float dot = 0.f;
+  f32x4 g[VPT], xv[VPT], dr[VPT];
 #pragma unroll
-  for (int v = 0; v < VPL; ++v) {
-    const int c = lane + 32 * v;
+  for (int v = 0; v < VPT; ++v) {
+    const int c = threadIdx.x + 128 * v;
     if (c < nvec) {
-      f32x4 dyv;
-      if constexpr (sizeof(TDY) == 2) {
-        const uint2 raw = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(dy) + base + 4 * c);
-        const float2 a = unpack_bf16x2(raw.x), b = unpack_bf16x2(raw.y);
-        dyv = f32x4{a.x, a.y, b.x, b.y};
-      } else {
-        dyv = *reinterpret_cast<const f32x4*>(reinterpret_cast<const float*>(dy) + base + 4 * c);
-      }
-      const f32x4 xv = *reinterpret_cast<const f32x4*>(x + base + 4 * c);
-      const f32x4 wv = *reinterpret_cast<const f32x4*>(w + 4 * c);
-      xh[v] = f32x4{xv.x * rs, xv.y * rs, xv.z * rs, xv.w * rs};
-      g[v] = f32x4{dyv.x * wv.x, dyv.y * wv.y, dyv.z * wv.z, dyv.w * wv.w};
-      dot += g[v].x * xh[v].x + g[v].y * xh[v].y + g[v].z * xh[v].z + g[v].w * xh[v].w;
+      g[v] = ld_dy4<TDY>(dy, base + 4 * c);
+      xv[v] = *reinterpret_cast<const f32x4*>(x + base + 4 * c);
+      if (dres_in) dr[v] = *reinterpret_cast<const f32x4*>(dres_in + base + 4 * c);
     }
   }
-  dot = warp_sum(dot) / (float)d;
+  float dot = 0.f;
 #pragma unroll
-  for (int v = 0; v < VPL; ++v) {
-    const int c = lane + 32 * v;
+  for (int v = 0; v < VPT; ++v) {
+    const int c = threadIdx.x + 128 * v;
     if (c < nvec) {
-      f32x4 o{rs * (g[v].x - xh[v].x * dot), rs * (g[v].y - xh[v].y * dot), rs * (g[v].z - xh[v].z * dot),
-              rs * (g[v].w - xh[v].w * dot)};
-      if (dres_in) {
-        const f32x4 dr = *reinterpret_cast<const f32x4*>(dres_in + base + 4 * c);
-        o.x += dr.x; o.y += dr.y; o.z += dr.z; o.w += dr.w;
-      }
+      const f32x4 wv = *reinterpret_cast<const f32x4*>(w + 4 * c);
+      g[v].x *= wv.x; g[v].y *= wv.y; g[v].z *= wv.z; g[v].w *= wv.w;
+      dot += g[v].x * xv[v].x + g[v].y * xv[v].y + g[v].z * xv[v].z + g[v].w * xv[v].w;
+    }
+  }
+  dot = block_sum(dot, red) * rs / (float)d;  // mean(g * xhat)
+  const float k2 = rs * rs * dot;             // rs*(g - xhat*dot) = rs*g - rs^2*dot*x
+#pragma unroll
+  for (int v = 0; v < VPT; ++v) {
+    const int c = threadIdx.x + 128 * v;
+    if (c < nvec) {
+      f32x4 o{rs * g[v].x - k2 * xv[v].x, rs * g[v].y - k2 * xv[v].y, rs * g[v].z - k2 * xv[v].z,
+              rs * g[v].w - k2 * xv[v].w};
+      if (dres_in) { o.x += dr[v].x; o.y += dr[v].y; o.z += dr[v].z; o.w += dr[v].w; }
       if (dx) *reinterpret_cast<f32x4*>(dx + base + 4 * c) = o;
       if (dx_bf16) *reinterpret_cast<uint2*>(dx_bf16 + base + 4 * c) = uint2{pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w)};
     }
@@ -187,18 +197,11 @@ __global__ void __launch_bounds__(128) rmsnorm_bwd_dw_kernel(const TDY* __restri
   const int r0 = blockIdx.y * rows_per_chunk;
   const int r1 = min(T, r0 + rows_per_chunk);
   f32x4 acc{0.f, 0.f, 0.f, 0.f};
-#pragma unroll 4
+#pragma unroll 8
   for (int r = r0; r < r1; ++r) {
-    const size_t base = (size_t)r * d + 4 * c;
-    f32x4 dyv;
-    if constexpr (sizeof(TDY) == 2) {
-      const uint2 raw = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(dy) + base);
-      const float2 a = unpack_bf16x2(raw.x), b = unpack_bf16x2(raw.y);
-      dyv = f32x4{a.x, a.y, b.x, b.y};
-    } else {
-      dyv = *reinterpret_cast<const f32x4*>(reinterpret_cast<const float*>(dy) + base);
-    }
-    const f32x4 xv = *reinterpret_cast<const f32x4*>(x + base);
+    const size_t off = (size_t)r * d + 4 * c;
+    const f32x4 dyv = ld_dy4<TDY>(dy, off);
+    const f32x4 xv = *reinterpret_cast<const f32x4*>(x + off);
     const float rs = rstd[r];
     acc.x += dyv.x * xv.x * rs; acc.y += dyv.y * xv.y * rs; acc.z += dyv.z * xv.z * rs; acc.w += dyv.w * xv.w * rs;
   }
@@ -293,20 +296,20 @@ extern "C" int b200_rmsnorm_bwd(const void* dy, int dy_dtype, const float* x, co
                          reinterpret_cast<uintptr_t>(dx_bf16)) & 15) == 0;
   if ((d % 8) == 0 && d <= 128 * 24 && aligned) {
     // fast path; the dw partial matrix has `chunks` <= workspace rows, so the scratch contract holds
-    const int rows_per_chunk = std::max(32, ceil_div(T, grid));
+    const int rows_per_chunk = std::max(16, ceil_div(T, grid));
     const int chunks = ceil_div(T, rows_per_chunk);
     const int fgrid = chunks;
 #define LAUNCH_W(TDY, VPL)                                                                                        \
-  rmsnorm_bwd_dx_kernel<TDY, VPL><<<ceil_div(T, 4), 128, 0, s>>>(reinterpret_cast<const TDY*>(dy), x, w, rstd,       \
+  rmsnorm_bwd_dx_kernel<TDY, VPL><<<T, 128, 0, s>>>(reinterpret_cast<const TDY*>(dy), x, w, rstd,       \
                                                                  dres_in, dx, dxb, T, d)
 #define BY_DT_W(VPL)                                                   \
   do {                                                                 \
     if (dy_dtype == B200_BF16) LAUNCH_W(__nv_bfloat16, VPL);           \
     else LAUNCH_W(float, VPL);                                         \
   } while (0)
-    if (d <= 128 * 8) BY_DT_W(8);
-    else if (d <= 128 * 16) BY_DT_W(16);
-    else BY_DT_W(24);
+    if (d <= 512 * 2) BY_DT_W(2);
+    else if (d <= 512 * 4) BY_DT_W(4);
+    else BY_DT_W(6);
 #undef BY_DT_W
 #undef LAUNCH_W
     B200_LAUNCH_CHECK();

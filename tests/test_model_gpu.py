@@ -91,3 +91,25 @@ def test_gradients_land_in_registered_slots():
     for n, p in model.named_parameters():
         assert lo <= p.grad.data_ptr() < hi, f"{n} gradient was not produced into its slot"
         grad_slots.unregister(p)
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_trainer_overlapped_optimizer_matches_plain(graph):
+    """Optimizer-in-backward (side stream) and the CUDA-graph step give the same trajectory as the plain loop."""
+    from cs336_a2_systems_b200.train import Trainer
+    base = _model(layers=2)
+    a, b = copy.deepcopy(base), copy.deepcopy(base)
+    ta = Trainer(a, AdamW(a.parameters(), lr=1e-3, weight_decay=0.1), cuda_graph=False, overlap_optimizer=False)
+    tb = Trainer(b, AdamW(b.parameters(), lr=1e-3, weight_decay=0.1), cuda_graph=graph, overlap_optimizer=True,
+                 overlap_unit_mb=0.5)
+    g = torch.Generator().manual_seed(3)
+    for step in range(8):
+        x = torch.randint(0, 1000, (2, 128), generator=g).cuda()
+        y = torch.roll(x, -1, 1)
+        la, lb = ta.step(x, y), tb.step(x, y)
+        assert abs(float(la) - float(lb)) < 1e-5, (step, float(la), float(lb))
+    torch.cuda.synchronize()
+    for (n, p), q in zip(a.named_parameters(), b.parameters()):
+        torch.testing.assert_close(p, q, rtol=1e-6, atol=1e-7, msg=n)
+    tb.optimizer.sync_step_from_device()
+    assert tb.optimizer.state[next(b.parameters())]["t"] == 9
