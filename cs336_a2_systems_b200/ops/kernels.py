@@ -244,7 +244,8 @@ class TensorTable:
             arr[i].shadow = sh.data_ptr() if sh is not None else 0
             arr[i].n = numel
             al = all(q % 16 == 0 for q in ptrs) and (sh is None or sh.data_ptr() % 8 == 0)
-            arr[i].aligned16 = int(al)
+            al32 = all(q % 32 == 0 for q in ptrs) and (sh is None or sh.data_ptr() % 16 == 0)
+            arr[i].aligned16 = 2 if al32 else int(al)
             starts.append(total)
             total += (numel + chunk - 1) // chunk
         dev = (grads[0] if grads[0] is not None else params[0]).device
@@ -280,10 +281,12 @@ class AdamWLaunch:
         row[:6] = torch.tensor(vals, dtype=torch.float32)
         self.hyper.copy_(row, non_blocking=True)
 
-    def launch(self) -> None:
-        check(_lib().b200_adamw_multi(p(self.tt.table), p(self.tt.starts), c_int(self.tt.n),
-                                      c_longlong(self.tt.total_chunks), p(self.hyper), p(self.step),
-                                      c_int(self.mode), c_int(1), stream_ptr()), "adamw_multi")
+    def launch(self, max_blocks: int = 0) -> None:
+        """``max_blocks`` caps the grid (0 = fill the GPU); a small cap keeps SM room for concurrent GEMMs."""
+        check(_lib().b200_adamw_multi_grid(p(self.tt.table), p(self.tt.starts), c_int(self.tt.n),
+                                           c_longlong(self.tt.total_chunks), p(self.hyper), p(self.step),
+                                           c_int(self.mode), c_int(1), c_int(max_blocks), stream_ptr()),
+              "adamw_multi")
         _count(2)
 
 

@@ -390,8 +390,8 @@ class AdamWPlan:
     def set_hyper(self, lr, b1, b2, eps, wd, grad_scale: float = 1.0) -> None:
         self._launch.set_hyper(lr, b1, b2, eps, wd, grad_scale)
 
-    def launch(self) -> None:
-        self._launch.launch()
+    def launch(self, max_blocks: int = 0) -> None:
+        self._launch.launch(max_blocks)
         for p_, sh in self._extra_shadows:  # a weight mirrored in several groups (rare)
             kernels.cast_bf16(p_.data, sh)
 

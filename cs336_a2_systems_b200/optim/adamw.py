@@ -98,7 +98,7 @@ class AdamW(torch.optim.Optimizer):
         return loss
 
     @torch.no_grad()
-    def step_subset(self, key, params) -> None:
+    def step_subset(self, key, params, max_blocks: int = 0) -> None:
         """Update only ``params`` now (one fused launch on the current stream); the next :meth:`step`
         skips them.  This is what lets a trainer run the optimizer for a layer on a side stream as soon
         as that layer's gradients are final, overlapped with the rest of backward ("optimizer in
@@ -119,11 +119,11 @@ class AdamW(torch.optim.Optimizer):
                 if not self._fusable(p):
                     self._step_param_torch(p, self.state[p], lr, b1, b2, eps, wd)
             if fus:
-                self._step_fused((gi, key), fus, lr, b1, b2, eps, wd)
+                self._step_fused((gi, key), fus, lr, b1, b2, eps, wd, max_blocks)
             self._done.update(id(p) for p in ps)
 
     # ------------------------------------------------------------------ fused sm_100a path
-    def _step_fused(self, gi: int, ps, lr, b1, b2, eps, wd):
+    def _step_fused(self, gi, ps, lr, b1, b2, eps, wd, max_blocks: int = 0):
         from ..ops import native
 
         for p in ps:
@@ -145,7 +145,7 @@ class AdamW(torch.optim.Optimizer):
                                     [self.state[p]["v"] for p in ps], key=key, step0=t0)
             self._plans[gi] = plan
         plan.set_hyper(lr, b1, b2, eps, wd)
-        plan.launch()
+        plan.launch(max_blocks)
         for p in ps:  # host mirror of the device step counter (exact outside CUDA-graph replay)
             self.state[p]["t"] += 1
 

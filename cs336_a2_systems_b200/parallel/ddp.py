@@ -175,8 +175,8 @@ class DDPBucketed(_DDPBase):
     :meth:`finish_gradient_synchronization` after ``backward()`` and before ``optimizer.step()``.
     """
 
-    #: element alignment of every gradient slot inside a bucket (16 B vectors for the kernels)
-    ALIGN_BYTES = 16
+    #: alignment of every gradient slot inside a bucket (256-bit vectors of the streaming optimizer kernel)
+    ALIGN_BYTES = 32
 
     def __init__(self, module: nn.Module, bucket_size_mb: float | None = None, process_group=None,
                  backend: str | None = None):

@@ -29,7 +29,7 @@ class GradArena:
     weight gradients are produced in place (stable addresses → CUDA-graph friendly, one flat
     buffer for clipping / the fused optimizer)."""
 
-    def __init__(self, params, align_elems: int = 4):
+    def __init__(self, params, align_elems: int = 8):  # 32-byte slots: the optimizer streams 256-bit vectors
         self.params = [p for p in params if p.requires_grad]
         total = 0
         self.offsets = []
@@ -60,6 +60,7 @@ class _OptimizerOverlap:
         self.device = device
         self.stream = torch.cuda.Stream(device=device)
         self._used = False
+        self.max_blocks = 2 * torch.cuda.get_device_properties(device).multi_processor_count
         if is_ddp and hasattr(model, "set_bucket_callback"):
             model.set_bucket_callback(self._on_bucket)
             self.units = None
@@ -94,7 +95,8 @@ class _OptimizerOverlap:
         ev.record(after_stream)
         self.stream.wait_event(ev)
         with torch.cuda.stream(self.stream):
-            self.optimizer.step_subset(key, params)
+            # two CTAs per SM: enough loads in flight to stream HBM, small enough to sit beside a GEMM CTA
+            self.optimizer.step_subset(key, params, max_blocks=self.max_blocks)
         self._used = True
 
     def _on_bucket(self, bucket_index: int, params, reduce_stream) -> None:

@@ -21,6 +21,22 @@ __device__ __forceinline__ int find_tensor(const long long* __restrict__ chunk_s
   return lo;
 }
 
+// 256-bit streaming accesses with L2 evict-first: optimizer traffic (30 B/param, touched once per step) must not
+// push the GEMM operands of a concurrently running backward pass out of the 126 MB L2.
+struct f32x8 { float v[8]; };
+__device__ __forceinline__ f32x8 ld_stream8(const float* p) {
+  f32x8 r;
+  asm volatile("ld.global.L1::no_allocate.L2::evict_first.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(r.v[0]), "=f"(r.v[1]), "=f"(r.v[2]), "=f"(r.v[3]), "=f"(r.v[4]), "=f"(r.v[5]), "=f"(r.v[6]), "=f"(r.v[7])
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void st_stream8(float* p, const f32x8& r) {
+  asm volatile("st.global.L1::no_allocate.L2::evict_first.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p),
+               "f"(r.v[0]), "f"(r.v[1]), "f"(r.v[2]), "f"(r.v[3]), "f"(r.v[4]), "f"(r.v[5]), "f"(r.v[6]), "f"(r.v[7])
+               : "memory");
+}
+
 // hyper: [lr, beta1, beta2, eps, weight_decay, grad_scale]; step: int (t of this update, starts at 1)
 // mode 0: course AdamW (alpha_t = lr*sqrt(1-b2^t)/(1-b1^t); p -= alpha_t*m/(sqrt(v)+eps); p -= lr*wd*p)
 // mode 1: torch.optim.AdamW (p *= 1-lr*wd; p -= lr/bc1 * m/(sqrt(v)/sqrt(bc2)+eps))
@@ -38,6 +54,42 @@ __global__ void __launch_bounds__(256) adamw_multi_kernel(const b200_adamw_tenso
     const b200_adamw_tensor td = table[ti];
     const long long off0 = (chunk - chunk_start[ti]) * kChunk;
     const bool vec = td.aligned16 != 0;
+    if (td.aligned16 >= 2 && off0 + kChunk <= td.n) {
+      // full chunk, every pointer 32-byte aligned: 2 x (256 threads x 8 elements), all loads issued up front
+      f32x8 P[2], G[2], M[2], V[2];
+#pragma unroll
+      for (int it = 0; it < 2; ++it) {
+        const long long i = off0 + ((long long)it * 256 + threadIdx.x) * 8;
+        P[it] = ld_stream8(td.p + i); G[it] = ld_stream8(td.g + i);
+        M[it] = ld_stream8(td.m + i); V[it] = ld_stream8(td.v + i);
+      }
+#pragma unroll
+      for (int it = 0; it < 2; ++it) {
+        const long long i = off0 + ((long long)it * 256 + threadIdx.x) * 8;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float gk = G[it].v[k] * gscale;
+          float mk = b1 * M[it].v[k] + (1.f - b1) * gk;
+          float vk = b2 * V[it].v[k] + (1.f - b2) * gk * gk;
+          float pk = P[it].v[k];
+          if (mode == 0) {
+            pk -= alpha_t * mk / (sqrtf(vk) + eps);
+            pk -= lr * wd * pk;
+          } else {
+            pk *= (1.f - lr * wd);
+            pk -= (lr / bc1) * mk / (sqrtf(vk) * rsqrt_bc2 + eps);
+          }
+          M[it].v[k] = mk; V[it].v[k] = vk; P[it].v[k] = pk;
+        }
+        st_stream8(td.p + i, P[it]); st_stream8(td.m + i, M[it]); st_stream8(td.v + i, V[it]);
+        if (td.shadow_bf16) {
+          u32x4 o{pack_bf16x2(P[it].v[0], P[it].v[1]), pack_bf16x2(P[it].v[2], P[it].v[3]),
+                  pack_bf16x2(P[it].v[4], P[it].v[5]), pack_bf16x2(P[it].v[6], P[it].v[7])};
+          *reinterpret_cast<u32x4*>(reinterpret_cast<__nv_bfloat16*>(td.shadow_bf16) + i) = o;
+        }
+      }
+      continue;
+    }
 #pragma unroll
     for (int it = 0; it < 4; ++it) {
       const long long i = off0 + ((long long)it * 256 + threadIdx.x) * 4;
@@ -163,19 +215,27 @@ using namespace b200;
 
 extern "C" int b200_adamw_chunk_elems(void) { return kChunk; }
 
-extern "C" int b200_adamw_multi(const b200_adamw_tensor* table_dev, const long long* chunk_start_dev, int n_tensors,
-                                long long total_chunks, const float* hyper_dev, int* step_dev, int mode,
-                                int increment_step, void* stream) {
+extern "C" int b200_adamw_multi_grid(const b200_adamw_tensor* table_dev, const long long* chunk_start_dev, int n_tensors,
+                                     long long total_chunks, const float* hyper_dev, int* step_dev, int mode,
+                                     int increment_step, int max_blocks, void* stream) {
   if (n_tensors <= 0 || total_chunks <= 0) return 0;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  adamw_multi_kernel<<<grid_for(total_chunks), 256, 0, s>>>(table_dev, chunk_start_dev, n_tensors, total_chunks,
-                                                            hyper_dev, step_dev, mode);
+  int grid = grid_for(total_chunks);
+  if (max_blocks > 0 && grid > max_blocks) grid = max_blocks;
+  adamw_multi_kernel<<<grid, 256, 0, s>>>(table_dev, chunk_start_dev, n_tensors, total_chunks, hyper_dev, step_dev, mode);
   B200_LAUNCH_CHECK();
   if (increment_step) {
     incr_step_kernel<<<1, 1, 0, s>>>(step_dev);
     B200_LAUNCH_CHECK();
   }
   return 0;
+}
+
+extern "C" int b200_adamw_multi(const b200_adamw_tensor* table_dev, const long long* chunk_start_dev, int n_tensors,
+                                long long total_chunks, const float* hyper_dev, int* step_dev, int mode,
+                                int increment_step, void* stream) {
+  return b200_adamw_multi_grid(table_dev, chunk_start_dev, n_tensors, total_chunks, hyper_dev, step_dev, mode,
+                               increment_step, 0, stream);
 }
 
 extern "C" int b200_gradnorm_partials(long long total_chunks) { return grid_for(total_chunks); }

@@ -106,7 +106,7 @@ typedef struct {
   float* v;
   void* shadow_bf16; /* nullable: bf16 copy of p refreshed by the update */
   long long n;
-  int aligned16; /* all pointers 16-byte aligned */
+  int aligned16; /* 0: unaligned, 1: all pointers 16-byte aligned, 2: all 32-byte aligned (256-bit streaming path) */
   int pad_;
 } b200_adamw_tensor;
 int b200_adamw_chunk_elems(void);
@@ -114,6 +114,11 @@ int b200_adamw_chunk_elems(void);
 int b200_adamw_multi(const b200_adamw_tensor* table_dev, const long long* chunk_start_dev, int n_tensors,
                      long long total_chunks, const float* hyper_dev, int* step_dev, int mode, int increment_step,
                      void* stream);
+/* Same with a cap on the grid (max_blocks > 0): a small footprint (e.g. 2 CTAs per SM) lets the update run
+ * on a side stream underneath backward GEMMs without crowding their CTAs out of the SMs. */
+int b200_adamw_multi_grid(const b200_adamw_tensor* table_dev, const long long* chunk_start_dev, int n_tensors,
+                          long long total_chunks, const float* hyper_dev, int* step_dev, int mode, int increment_step,
+                          int max_blocks, void* stream);
 int b200_gradnorm_partials(long long total_chunks);
 int b200_clip_grad_norm(const b200_adamw_tensor* table_dev, const long long* chunk_start_dev, int n_tensors,
                         long long total_chunks, float max_norm, float eps, float* partial_dev, float* norm_out_dev,
