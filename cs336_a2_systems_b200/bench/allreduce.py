@@ -39,7 +39,7 @@ def main():
     ap.add_argument("--sizes-mb", type=float, nargs="+", default=[0.008, 0.064, 0.5, 1, 10, 100, 1000])
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--iters", type=int, default=10)
-    ap.add_argument("--blocks", type=int, default=16)
+    ap.add_argument("--blocks", type=int, default=0)
     ap.add_argument("--json", default=None)
     args = ap.parse_args()
     dev = setup()

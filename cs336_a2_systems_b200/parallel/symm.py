@@ -27,7 +27,7 @@ import torch
 import torch.distributed as dist
 
 _ONE_SHOT_MAX_BYTES = int(os.environ.get("B200SYS_ONESHOT_MAX", 512 * 1024))
-_COMM_BLOCKS = int(os.environ.get("B200SYS_COMM_BLOCKS", 16))
+_COMM_BLOCKS = int(os.environ.get("B200SYS_COMM_BLOCKS", 0))  # 0: kernel default (16 small / 48 large)
 _ALGO = int(os.environ.get("B200SYS_ALLREDUCE_ALGO", 0))  # 0 auto, 1 one-shot, 2 two-shot, 3 multimem
 
 
@@ -71,6 +71,8 @@ class SymmArena:
         self.rank = dist.get_rank(self.group)
         self.world_size = dist.get_world_size(self.group)
         nbytes = (nbytes + 255) // 256 * 256
+        if symm_mem.get_signal_pad_size() < 16384:
+            symm_mem.set_signal_pad_size(16384)  # room for two slots of 64 blocks x 8 ranks flag words
         self.bytes = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
         self.bytes.zero_()
         self.handle = symm_mem.rendezvous(self.bytes, self.group.group_name)

@@ -1,4 +1,7 @@
-"""Training: the step loop (eager or CUDA-graph), synthetic data, checkpointing, CLI drivers."""
+"""Training: the step loop (eager or CUDA-graph), drivers for every DDP flavour, synthetic data, checkpoints."""
+from .checkpoint import load_checkpoint, save_checkpoint
+from .data import SyntheticBatches, generate_random_data, get_batch, set_seed
 from .trainer import GradArena, Trainer
 
-__all__ = ["Trainer", "GradArena"]
+__all__ = ["Trainer", "GradArena", "save_checkpoint", "load_checkpoint", "get_batch", "SyntheticBatches",
+           "generate_random_data", "set_seed"]

@@ -119,6 +119,11 @@ class Trainer:
         self.cuda_graph = cuda_graph
         self.device = next(model.parameters()).device
         self._is_ddp = hasattr(model, "finish_gradient_synchronization")
+        red = getattr(model, "_reducer", None)
+        if self.cuda_graph and red is not None and getattr(red, "kind", "") == "c10d":
+            # torch.distributed collectives inside a captured step are not supported by this trainer (the NCCL
+            # path hung under capture on B200); the NVLink backend's kernels are plain launches and capture fine
+            self.cuda_graph = False
         self.arena = None
         if grad_arena or (grad_arena is None and self.device.type == "cuda" and not self._is_ddp):
             self.arena = GradArena(list(model.parameters()))

@@ -25,7 +25,7 @@ namespace comm {
 
 constexpr int kMaxRanks = 8;
 constexpr int kThreads = 512;
-constexpr int kMaxBlocks = 32;
+constexpr int kMaxBlocks = 64;
 
 struct Peers {
   void* ptr[kMaxRanks];
@@ -116,26 +116,84 @@ __global__ void __launch_bounds__(kThreads) allreduce_oneshot_kernel(Peers P, lo
   }
 }
 
+// ---- 256-bit helpers (bandwidth paths) ---------------------------------------------------------
+struct v8f { float f[8]; };
+__device__ __forceinline__ v8f ld_peer8(const void* p) {
+  v8f r;
+  asm volatile("ld.global.relaxed.sys.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(r.f[0]), "=f"(r.f[1]), "=f"(r.f[2]), "=f"(r.f[3]), "=f"(r.f[4]), "=f"(r.f[5]), "=f"(r.f[6]), "=f"(r.f[7])
+               : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ void st_peer8(void* p, const v8f& r) {
+  asm volatile("st.global.relaxed.sys.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(r.f[0]), "f"(r.f[1]),
+               "f"(r.f[2]), "f"(r.f[3]), "f"(r.f[4]), "f"(r.f[5]), "f"(r.f[6]), "f"(r.f[7]) : "memory");
+}
+template <bool BF16> struct Vec8;
+template <> struct Vec8<false> {
+  static constexpr int N = 8;
+  static __device__ __forceinline__ void add(float (&acc)[16], const v8f& v) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] += v.f[k];
+  }
+  static __device__ __forceinline__ v8f finish(const float (&acc)[16], float s) {
+    v8f o;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) o.f[k] = acc[k] * s;
+    return o;
+  }
+};
+template <> struct Vec8<true> {
+  static __device__ __forceinline__ void add(float (&acc)[16], const v8f& v) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { const float2 f = unpack_bf16x2(__float_as_uint(v.f[k])); acc[2 * k] += f.x; acc[2 * k + 1] += f.y; }
+  }
+  static __device__ __forceinline__ v8f finish(const float (&acc)[16], float s) {
+    v8f o;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) o.f[k] = __uint_as_float(pack_bf16x2(acc[2 * k] * s, acc[2 * k + 1] * s));
+    return o;
+  }
+};
+
 // ---- two-shot --------------------------------------------------------------------------------
-template <bool BF16>
-__global__ void __launch_bounds__(kThreads) allreduce_twoshot_kernel(Peers P, long long byte_off, long long nvec,
+// 32-byte vectors, U vectors per thread per trip with all WS*U peer loads issued before the first add:
+// NVLink round trips are ~2 us, so bandwidth is bought with bytes in flight (grid x 512 threads x U x 32 B per peer).
+template <bool BF16, int WS>
+__global__ void __launch_bounds__(kThreads) allreduce_twoshot_kernel(Peers P, long long byte_off, long long nvec32,
                                                                      float scale, int rank, int ws, int slot) {
+  constexpr int U = WS <= 2 ? 4 : (WS <= 4 ? 2 : 1);
   cross_rank_barrier(P, rank, ws, slot);
-  const long long per = (nvec + ws - 1) / ws;
-  const long long lo = per * rank, hi = (lo + per < nvec) ? lo + per : nvec;
-  for (long long i = lo + (long long)blockIdx.x * kThreads + threadIdx.x; i < hi; i += (long long)gridDim.x * kThreads) {
-    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    f32x4 v[kMaxRanks];
+  const long long per = (nvec32 + ws - 1) / ws;
+  const long long lo = per * rank, hi = (lo + per < nvec32) ? lo + per : nvec32;
+  const long long stride = (long long)gridDim.x * kThreads;
+  for (long long i0 = lo + (long long)blockIdx.x * kThreads + threadIdx.x; i0 < hi; i0 += stride * U) {
+    v8f v[WS][U];
 #pragma unroll
-    for (int r = 0; r < kMaxRanks; ++r)
-      if (r < ws) v[r] = ld_peer(static_cast<const char*>(P.ptr[r]) + byte_off + i * 16);
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < hi) {
 #pragma unroll
-    for (int r = 0; r < kMaxRanks; ++r)
-      if (r < ws) Vec<BF16>::add(acc, v[r]);
-    const f32x4 out = Vec<BF16>::finish(acc, scale);
+        for (int r = 0; r < WS; ++r)
+          if (r < ws) v[r][u] = ld_peer8(static_cast<const char*>(P.ptr[r]) + byte_off + i * 32);
+      }
+    }
 #pragma unroll
-    for (int r = 0; r < kMaxRanks; ++r)
-      if (r < ws) st_peer(static_cast<char*>(P.ptr[r]) + byte_off + i * 16, out);
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < hi) {
+        float acc[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) acc[k] = 0.f;
+#pragma unroll
+        for (int r = 0; r < WS; ++r)
+          if (r < ws) Vec8<BF16>::add(acc, v[r][u]);
+        const v8f out = Vec8<BF16>::finish(acc, scale);
+#pragma unroll
+        for (int r = 0; r < WS; ++r)
+          if (r < ws) st_peer8(static_cast<char*>(P.ptr[r]) + byte_off + i * 32, out);
+      }
+    }
   }
   cross_rank_barrier(P, rank, ws, slot);  // all slices have landed everywhere
 }
@@ -145,24 +203,41 @@ template <bool BF16>
 __global__ void __launch_bounds__(kThreads) allreduce_multimem_kernel(Peers P, char* mc, long long byte_off,
                                                                       long long nvec, float scale, int rank, int ws,
                                                                       int slot) {
+  constexpr int U = 4;
   cross_rank_barrier(P, rank, ws, slot);
   const long long per = (nvec + ws - 1) / ws;
   const long long lo = per * rank, hi = (lo + per < nvec) ? lo + per : nvec;
-  for (long long i = lo + (long long)blockIdx.x * kThreads + threadIdx.x; i < hi; i += (long long)gridDim.x * kThreads) {
-    char* a = mc + byte_off + i * 16;
-    if constexpr (!BF16) {
-      float x, y, z, w;
-      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
-                   : "=f"(x), "=f"(y), "=f"(z), "=f"(w) : "l"(a) : "memory");
-      x *= scale; y *= scale; z *= scale; w *= scale;
-      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(a), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
-    } else {
-      uint32_t u[4];
-      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
-                   : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]) : "l"(a) : "memory");
+  const long long stride = (long long)gridDim.x * kThreads;
+  for (long long i0 = lo + (long long)blockIdx.x * kThreads + threadIdx.x; i0 < hi; i0 += stride * U) {
+    uint32_t u[U][4];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) { const float2 f = unpack_bf16x2(u[k]); u[k] = pack_bf16x2(f.x * scale, f.y * scale); }
-      asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};" ::"l"(a), "r"(u[0]), "r"(u[1]), "r"(u[2]), "r"(u[3]) : "memory");
+    for (int q = 0; q < U; ++q) {
+      const long long i = i0 + q * stride;
+      if (i < hi) {
+        char* a = mc + byte_off + i * 16;
+        if constexpr (!BF16)
+          asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                       : "=r"(u[q][0]), "=r"(u[q][1]), "=r"(u[q][2]), "=r"(u[q][3]) : "l"(a) : "memory");
+        else
+          asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                       : "=r"(u[q][0]), "=r"(u[q][1]), "=r"(u[q][2]), "=r"(u[q][3]) : "l"(a) : "memory");
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      const long long i = i0 + q * stride;
+      if (i < hi) {
+        char* a = mc + byte_off + i * 16;
+        if constexpr (!BF16) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) u[q][k] = __float_as_uint(__uint_as_float(u[q][k]) * scale);
+          asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(a), "r"(u[q][0]), "r"(u[q][1]), "r"(u[q][2]), "r"(u[q][3]) : "memory");
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) { const float2 f = unpack_bf16x2(u[q][k]); u[q][k] = pack_bf16x2(f.x * scale, f.y * scale); }
+          asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};" ::"l"(a), "r"(u[q][0]), "r"(u[q][1]), "r"(u[q][2]), "r"(u[q][3]) : "memory");
+        }
+      }
     }
   }
   cross_rank_barrier(P, rank, ws, slot);
@@ -200,7 +275,7 @@ extern "C" int b200_allreduce(const unsigned long long* peer_ptrs_host, const un
   const long long nvec = (nbytes + 15) / 16;  // buckets are padded to 16 bytes by the allocator
   Peers P;
   if (int rc = load_peers(peer_ptrs_host, signal_ptrs_host, world_size, &P)) return rc;
-  if (blocks <= 0) blocks = 16;
+  if (blocks <= 0) blocks = nbytes >= (8 << 20) ? 48 : 16;
   if (blocks > kMaxBlocks) blocks = kMaxBlocks;
   const long long want = (nvec + kThreads - 1) / kThreads;
   if (want < blocks) blocks = (int)(want < 1 ? 1 : want);
@@ -214,10 +289,15 @@ extern "C" int b200_allreduce(const unsigned long long* peer_ptrs_host, const un
       if (bf) allreduce_oneshot_kernel<true><<<blocks, kThreads, 0, s>>>(P, byte_off, nvec, scale, rank, world_size, signal_slot);
       else allreduce_oneshot_kernel<false><<<blocks, kThreads, 0, s>>>(P, byte_off, nvec, scale, rank, world_size, signal_slot);
       break;
-    case 2:
-      if (bf) allreduce_twoshot_kernel<true><<<blocks, kThreads, 0, s>>>(P, byte_off, nvec, scale, rank, world_size, signal_slot);
-      else allreduce_twoshot_kernel<false><<<blocks, kThreads, 0, s>>>(P, byte_off, nvec, scale, rank, world_size, signal_slot);
+    case 2: {
+      const long long nvec32 = (nbytes + 31) / 32;  // slots are 256-byte padded: whole 32-byte vectors are ours
+#define TWOSHOT(BFV, WSV) allreduce_twoshot_kernel<BFV, WSV><<<blocks, kThreads, 0, s>>>(P, byte_off, nvec32, scale, rank, world_size, signal_slot)
+      if (world_size <= 2) { if (bf) TWOSHOT(true, 2); else TWOSHOT(false, 2); }
+      else if (world_size <= 4) { if (bf) TWOSHOT(true, 4); else TWOSHOT(false, 4); }
+      else { if (bf) TWOSHOT(true, 8); else TWOSHOT(false, 8); }
+#undef TWOSHOT
       break;
+    }
     case 3:
       if (bf) allreduce_multimem_kernel<true><<<blocks, kThreads, 0, s>>>(P, static_cast<char*>(multicast_ptr), byte_off, nvec, scale, rank, world_size, signal_slot);
       else allreduce_multimem_kernel<false><<<blocks, kThreads, 0, s>>>(P, static_cast<char*>(multicast_ptr), byte_off, nvec, scale, rank, world_size, signal_slot);
