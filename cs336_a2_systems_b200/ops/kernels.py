@@ -354,6 +354,10 @@ def fa2_bwd(q, k, v, o, lse, do, causal: bool, dq=None, dk=None, dv=None, rope_c
 # ------------------------------------------------------------------------------------------------
 # NVLink collectives
 # ------------------------------------------------------------------------------------------------
+import os as _os
+
+_MULTIMEM_AUTO = _os.environ.get("B200SYS_MULTIMEM", "1") == "1"
+
 def host_ptr_array(ptrs):
     """ctypes array of device addresses (the C ABI takes peer tables as small host arrays)."""
     return (ctypes.c_ulonglong * len(ptrs))(*[int(x) for x in ptrs])
@@ -364,9 +368,11 @@ def allreduce_avg(arena, byte_off: int, numel: int, dtype: torch.dtype, one_shot
     """In-place average over ranks of ``numel`` elements at ``byte_off`` of the symmetric arena."""
     es = 2 if dtype == torch.bfloat16 else 4
     if algo == 0:
+        # measured on B200/NVSwitch (profiles/allreduce_*.json): one-shot only wins for tiny messages; with two
+        # ranks the P2P two-shot beats the NVLS path, with more ranks the in-switch reduction moves fewer bytes
         if numel * es <= one_shot_max:
             algo = 1
-        elif arena.multicast_ptr:
+        elif arena.multicast_ptr and arena.world_size > 2 and _MULTIMEM_AUTO:
             algo = 3
         else:
             algo = 2

@@ -26,7 +26,7 @@ import os
 import torch
 import torch.distributed as dist
 
-_ONE_SHOT_MAX_BYTES = int(os.environ.get("B200SYS_ONESHOT_MAX", 512 * 1024))
+_ONE_SHOT_MAX_BYTES = int(os.environ.get("B200SYS_ONESHOT_MAX", 64 * 1024))
 _COMM_BLOCKS = int(os.environ.get("B200SYS_COMM_BLOCKS", 0))  # 0: kernel default (16 small / 48 large)
 _ALGO = int(os.environ.get("B200SYS_ALLREDUCE_ALGO", 0))  # 0 auto, 1 one-shot, 2 two-shot, 3 multimem
 

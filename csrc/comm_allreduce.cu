@@ -280,7 +280,7 @@ extern "C" int b200_allreduce(const unsigned long long* peer_ptrs_host, const un
   const long long want = (nvec + kThreads - 1) / kThreads;
   if (want < blocks) blocks = (int)(want < 1 ? 1 : want);
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  if (algo == 0) algo = nbytes <= 256 * 1024 ? 1 : (multicast_ptr ? 3 : 2);
+  if (algo == 0) algo = nbytes <= 64 * 1024 ? 1 : ((multicast_ptr && world_size > 2) ? 3 : 2);
   if (algo == 1 && nvec > (long long)blocks * kThreads * kOneShotVecs) algo = 2;  // does not fit in registers
   if (algo == 3 && !multicast_ptr) algo = 2;
   const bool bf = dtype == B200_BF16;
