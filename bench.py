@@ -43,6 +43,9 @@ def parse_args():
     ap.add_argument("--bucket-mb", type=float, default=100.0)
     ap.add_argument("--no-graph", action="store_true", help="ours: do not capture the step in a CUDA graph")
     ap.add_argument("--comm", default=None, help="ours: gradient backend override (symm | c10d)")
+    ap.add_argument("--sharded", action="store_true",
+                    help="shard optimizer state across ranks (ours: ShardedOptimizer + fused NVLink AdamW/distribute; "
+                         "reference: ShardedStateOptimizer)")
     ap.add_argument("--no-overlap", action="store_true",
                     help="ours: run the optimizer after backward instead of overlapping it with backward")
     return ap.parse_args()
@@ -115,9 +118,16 @@ def build_ours(args, rank, ws, dev):
     model = build_lm(args.model, vocab_size=args.vocab, context_length=args.ctx, device=dev)
     if ws > 1:
         model = DDPBucketed(model, bucket_size_mb=args.bucket_mb, backend=args.comm)
-    opt = AdamW(model.parameters(), lr=1e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
-    trainer = Trainer(model, opt, autocast=True, cuda_graph=not args.no_graph,
-                      overlap_optimizer=not args.no_overlap)
+    kw = dict(lr=1e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
+    fused_sharded = False
+    if args.sharded and ws > 1:
+        from cs336_a2_systems_b200.parallel import ShardedOptimizer
+        opt = ShardedOptimizer(model.parameters(), AdamW, **kw)
+        fused_sharded = opt.enable_symmetric()
+    else:
+        opt = AdamW(model.parameters(), **kw)
+    trainer = Trainer(model, opt, autocast=True, cuda_graph=not args.no_graph and not (args.sharded and ws > 1),
+                      overlap_optimizer=not args.no_overlap and not args.sharded)
     state = {"launches_per_step": 0}
 
     def step_device(x, y):
@@ -131,7 +141,8 @@ def build_ours(args, rank, ws, dev):
         trainer._step_eager(x, y)
         state["launches_per_step"] = kernels.launches - n0
 
-    extra = {"cuda_graph": not args.no_graph, "optimizer_overlapped_with_backward": not args.no_overlap,
+    extra = {"cuda_graph": trainer.cuda_graph, "optimizer_overlapped_with_backward": trainer._overlap is not None,
+             "sharded_optimizer": bool(args.sharded and ws > 1), "fused_nvlink_sharded_adamw": fused_sharded,
              "comm": getattr(getattr(model, "_reducer", None), "kind", "none")}
     return step_device, step_e2e, count_launches, state, extra
 
@@ -153,7 +164,11 @@ def build_reference(args, rank, ws, dev):
                                         rope_theta=10000.0)
     model = model.to(dev)
     ddp = ref.DDP_Bucketed(model, bucket_size_mb=args.bucket_mb) if ws > 1 else None
-    opt = ref.AdamW(model.parameters(), lr=1e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
+    kw = dict(lr=1e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
+    if args.sharded and ws > 1:
+        opt = ref.ShardedStateOptimizer(model.parameters(), ref.AdamW, **kw)
+    else:
+        opt = ref.AdamW(model.parameters(), **kw)
     fwd = ddp if ddp is not None else model
 
     def step_device(x, y):
@@ -174,7 +189,7 @@ def build_reference(args, rank, ws, dev):
         y = yh.to(dev, non_blocking=True)
         return float(step_device(x, y).item())
 
-    return step_device, step_e2e, None, {"launches_per_step": None}, {}
+    return step_device, step_e2e, None, {"launches_per_step": None}, {"sharded_optimizer": bool(args.sharded and ws > 1)}
 
 
 def main():
@@ -236,8 +251,8 @@ def main():
         from cs336_a2_systems_b200.models import get_model_config
         cfg = get_model_config(args.model)
         out = {
-            "metric": "XL LM train tokens/s (bucketed DDP, bf16 autocast, AdamW)" if args.model == "xl"
-                      else f"{args.model} LM train tokens/s",
+            "metric": "XL LM train tokens/s (bucketed DDP, bf16 autocast, AdamW)" if args.model == "xl" and not args.sharded
+                      else f"{args.model} LM train tokens/s" + (" (DDP + sharded optimizer)" if args.sharded else ""),
             "value": round(value, 1), "unit": "tokens/s", "n_gpus": ws, "steps": args.steps, "warmup": n_warm,
             "ms_per_step": round(ms_per_step, 3), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic tokens, random-init weights",
