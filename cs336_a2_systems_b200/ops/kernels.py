@@ -19,7 +19,7 @@ from .._native import check, p, stream_ptr
 BF16, F32 = 0, 1
 _DT = {torch.bfloat16: BF16, torch.float32: F32}
 
-EPI_BF16, EPI_F32, EPI_F32_ACC, EPI_BF16_SWIGLU, EPI_F32_RESID, EPI_BF16_ROPE = 0, 1, 2, 3, 4, 5
+EPI_BF16, EPI_F32, EPI_F32_ACC, EPI_BF16_SWIGLU, EPI_F32_RESID, EPI_BF16_ROPE, EPI_F32_T = 0, 1, 2, 3, 4, 5, 6
 
 #: launch counter (kernels launched through this module), for bench.py's "gpu_launches"
 launches = 0
@@ -47,6 +47,18 @@ def gemm_supported(a: Tensor, b: Tensor) -> bool:
     return True
 
 
+def wgrad(dy: Tensor, x: Tensor, out: Tensor | None = None) -> Tensor:
+    """``dW[N_out, K_in] = dyᵀ · x`` (fp32).  A tall result (N_out > K_in) is computed as its wide transpose
+    ``xᵀ · dy`` with the transposed-store epilogue: the tile-width dimension gets the long side (256-wide
+    tiles run ~1.4x faster than 128-wide ones) and the stores are fully coalesced."""
+    n_out, k_in = dy.shape[1], x.shape[1]
+    if n_out > k_in:
+        if out is None:
+            out = torch.empty(n_out, k_in, dtype=torch.float32, device=dy.device)
+        return gemm(x, dy, a_mn=True, b_mn=True, epilogue=EPI_F32_T, out=out)
+    return gemm(dy, x, a_mn=True, b_mn=True, epilogue=EPI_F32, out=out)
+
+
 def gemm(a: Tensor, b: Tensor, *, a_mn: bool = False, b_mn: bool = False, epilogue: int = EPI_BF16,
          out: Tensor | None = None, aux: Tensor | None = None, force_bn: int = 0,
          rope: tuple | None = None) -> Tensor:
@@ -67,11 +79,12 @@ def gemm(a: Tensor, b: Tensor, *, a_mn: bool = False, b_mn: bool = False, epilog
     if not gemm_supported(a, b):
         raise ValueError("gemm: operands must be bf16, 2-D, unit inner stride, 16-byte aligned rows")
     n_out = N // 2 if epilogue == EPI_BF16_SWIGLU else N
+    out_shape = (N, M) if epilogue == EPI_F32_T else (M, n_out)
     if out is None:
         dt = torch.bfloat16 if epilogue in (EPI_BF16, EPI_BF16_SWIGLU, EPI_BF16_ROPE) else torch.float32
-        out = torch.empty(M, n_out, dtype=dt, device=a.device)
+        out = torch.empty(out_shape, dtype=dt, device=a.device)
     else:
-        assert out.shape == (M, n_out) and out.stride(1) == 1
+        assert tuple(out.shape) == out_shape and out.stride(1) == 1
     ld_aux = aux.stride(0) if (aux is not None and rope is None) else 0
     check(_lib().b200_gemm_bf16_ex(p(a), p(b), p(out), p(aux), c_int(M), c_int(N), c_int(K), c_int(a.stride(0)),
                                    c_int(b.stride(0)), c_int(out.stride(0)), c_int(ld_aux), c_int(int(a_mn)),
@@ -327,6 +340,9 @@ def fa2_fwd(q: Tensor, k: Tensor, v: Tensor, causal: bool, out: Tensor | None = 
     return out, lse
 
 
+_dq_workspaces: dict = {}
+
+
 def fa2_bwd(q, k, v, o, lse, do, causal: bool, dq=None, dk=None, dv=None, rope_cache: Tensor | None = None):
     """``rope_cache``: when q,k were rotated before attention, un-rotate dq,dk on the way out (fused)."""
     B, H, Nq, D = q.shape
@@ -337,16 +353,22 @@ def fa2_bwd(q, k, v, o, lse, do, causal: bool, dq=None, dk=None, dv=None, rope_c
     dk = torch.empty_like(k) if dk is None else dk
     dv = torch.empty_like(v) if dv is None else dv
     delta = torch.empty(B, H, Nq, dtype=torch.float32, device=q.device)
-    dq_acc = torch.empty(B, H, Nq, D, dtype=torch.float32, device=q.device)
+    # fp32 dQ accumulator: one zeroed workspace per shape, handed back zeroed by the kernel's last pass
+    # (calls of the same shape are assumed to be stream-ordered, as they are in a training step)
+    key = (q.device, B, H, Nq, D)
+    dq_acc = _dq_workspaces.get(key)
+    if dq_acc is None:
+        dq_acc = torch.zeros(B, H, Nq, D, dtype=torch.float32, device=q.device)
+        _dq_workspaces[key] = dq_acc
     rope_ctx = 0
     if rope_cache is not None:
         assert rope_cache.dtype == torch.float32 and rope_cache.is_contiguous() and rope_cache.shape[2] * 2 == D
         rope_ctx = rope_cache.shape[1]
-    check(_lib().b200_fa2_bwd_rope(p(q), p(k), p(v), p(o), p(lse), p(do), p(dq), p(dk), p(dv), p(delta), p(dq_acc),
+    check(_lib().b200_fa2_bwd_ex(p(q), p(k), p(v), p(o), p(lse), p(do), p(dq), p(dk), p(dv), p(delta), p(dq_acc),
                                    c_int(B), c_int(H), c_int(Nq), c_int(Nk), c_int(D), _strides3(q), _strides3(k),
                                    _strides3(v), _strides3(o), _strides3(do), _strides3(dq), _strides3(dk),
                                    _strides3(dv), c_int(int(causal)), c_float(1.0 / (D ** 0.5)), p(rope_cache),
-                                   c_int(rope_ctx), stream_ptr()), "fa2_bwd")
+                                   c_int(rope_ctx), c_int(1), stream_ptr()), "fa2_bwd")
     _count(4)
     return dq, dk, dv
 

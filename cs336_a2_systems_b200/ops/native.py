@@ -157,7 +157,7 @@ class LinearFn(torch.autograd.Function):
         if len(ws) > 1 and all(need):
             joint = grad_slots.claim_group(ws)
             if joint is not None:
-                kernels.gemm(dy2, x2, a_mn=True, b_mn=True, epilogue=kernels.EPI_F32, out=joint)
+                kernels.wgrad(dy2, x2, out=joint)
                 dws, r0 = [], 0
                 for w in ws:
                     dws.append(joint[r0:r0 + w.shape[0]])
@@ -172,7 +172,7 @@ class LinearFn(torch.autograd.Function):
                 dyi = dy2[:, r0:r0 + n_i]  # column slice: MN-major A operand with lda = N
                 if dyi.data_ptr() % 16 != 0:
                     dyi = dyi.contiguous()
-                dws.append(kernels.gemm(dyi, x2, a_mn=True, b_mn=True, epilogue=kernels.EPI_F32, out=dst))
+                dws.append(kernels.wgrad(dyi, x2, out=dst))
             else:
                 dws.append(None)
             r0 += n_i

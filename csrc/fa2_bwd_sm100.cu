@@ -53,6 +53,7 @@ struct BwdParams {
   int num_q_tiles;
   const float* rope_cache;  // nullable: (2, rope_ctx, D/2) cos/sin (used by the dq/dk post-passes)
   int rope_ctx;
+  int rope_epilogue;  // 1: dK is un-rotated in the kernel epilogue (head dim 64); 0: by the post-pass
 };
 
 __device__ __forceinline__ uint32_t swz_off_b(int row, int col, int rows) {
@@ -304,6 +305,30 @@ fa2_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 #pragma unroll
           for (int i = 0; i < 32; ++i) t[i] = 0u;
         }
+        if (which == 1 && p.rope_epilogue && key < p.Nk) {
+          // dK was computed w.r.t. the rotated keys: rotate back by -angle(position = key index).  The 16 angles
+          // of this 32-column chunk are contiguous in the cache: eight vector loads issued together.
+          const int half = p.D >> 1;
+          const float* cosr = p.rope_cache + (size_t)key * half + c * 16;
+          const float* sinr = p.rope_cache + (size_t)p.rope_ctx * half + (size_t)key * half + c * 16;
+          f32x4 cs[4], sn[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            cs[q] = *reinterpret_cast<const f32x4*>(cosr + 4 * q);
+            sn[q] = *reinterpret_cast<const f32x4*>(sinr + 4 * q);
+          }
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float c4[4] = {cs[q].x, cs[q].y, cs[q].z, cs[q].w}, s4[4] = {sn[q].x, sn[q].y, sn[q].z, sn[q].w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int i = 4 * q + e;
+              const float a = __uint_as_float(t[2 * i]), b = __uint_as_float(t[2 * i + 1]);
+              t[2 * i] = __float_as_uint(c4[e] * a + s4[e] * b);
+              t[2 * i + 1] = __float_as_uint(c4[e] * b - s4[e] * a);
+            }
+          }
+        }
         if (key < p.Nk) {
           if (vec) {
 #pragma unroll
@@ -360,7 +385,7 @@ __global__ void fa2_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv
 
 __global__ void fa2_dq_convert_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dq, int H, int Nq,
                                       int D, long long sb, long long sh, long long sr, long long total,
-                                      const float* __restrict__ rope_cache, int rope_ctx) {
+                                      const float* __restrict__ rope_cache, int rope_ctx, int rezero) {
   const long long idx = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 2;
   if (idx >= total) return;
   const int d = (int)(idx % D);
@@ -370,6 +395,7 @@ __global__ void fa2_dq_convert_kernel(const float* __restrict__ acc, __nv_bfloat
   const int hh = (int)(bh % H);
   const long long bb = bh / H;
   float2 v = *reinterpret_cast<const float2*>(acc + idx);
+  if (rezero) *reinterpret_cast<float2*>(const_cast<float*>(acc) + idx) = make_float2(0.f, 0.f);  // ready for the next call
   if (rope_cache != nullptr) {  // un-rotate the pair (d, d+1) by the angle of position i
     const int half = D >> 1;
     const float cs = rope_cache[(size_t)i * half + (d >> 1)];
@@ -418,12 +444,12 @@ static int launch_bwd(const CUtensorMap& q, const CUtensorMap& k, const CUtensor
 }  // namespace fa2
 }  // namespace b200
 
-extern "C" int b200_fa2_bwd_rope(const void* q, const void* k, const void* v, const void* o, const float* lse,
-                                 const void* dout, void* dq, void* dk, void* dv, float* delta, float* dq_acc, int B,
-                                 int H, int Nq, int Nk, int D, const long long* q_strides, const long long* k_strides,
-                                 const long long* v_strides, const long long* o_strides, const long long* do_strides,
-                                 const long long* dq_strides, const long long* dk_strides, const long long* dv_strides,
-                                 int causal, float scale, const float* rope_cache, int rope_ctx, void* stream);
+extern "C" int b200_fa2_bwd_ex(const void* q, const void* k, const void* v, const void* o, const float* lse,
+                               const void* dout, void* dq, void* dk, void* dv, float* delta, float* dq_acc, int B,
+                               int H, int Nq, int Nk, int D, const long long* q_strides, const long long* k_strides,
+                               const long long* v_strides, const long long* o_strides, const long long* do_strides,
+                               const long long* dq_strides, const long long* dk_strides, const long long* dv_strides,
+                               int causal, float scale, const float* rope_cache, int rope_ctx, int flags, void* stream);
 
 extern "C" int b200_fa2_bwd(const void* q, const void* k, const void* v, const void* o, const float* lse,
                             const void* dout, void* dq, void* dk, void* dv, float* delta, float* dq_acc, int B, int H,
@@ -431,17 +457,17 @@ extern "C" int b200_fa2_bwd(const void* q, const void* k, const void* v, const v
                             const long long* v_strides, const long long* o_strides, const long long* do_strides,
                             const long long* dq_strides, const long long* dk_strides, const long long* dv_strides,
                             int causal, float scale, void* stream) {
-  return b200_fa2_bwd_rope(q, k, v, o, lse, dout, dq, dk, dv, delta, dq_acc, B, H, Nq, Nk, D, q_strides, k_strides,
-                           v_strides, o_strides, do_strides, dq_strides, dk_strides, dv_strides, causal, scale, nullptr,
-                           0, stream);
+  return b200_fa2_bwd_ex(q, k, v, o, lse, dout, dq, dk, dv, delta, dq_acc, B, H, Nq, Nk, D, q_strides, k_strides,
+                         v_strides, o_strides, do_strides, dq_strides, dk_strides, dv_strides, causal, scale, nullptr, 0,
+                         0, stream);
 }
 
-extern "C" int b200_fa2_bwd_rope(const void* q, const void* k, const void* v, const void* o, const float* lse,
+extern "C" int b200_fa2_bwd_ex(const void* q, const void* k, const void* v, const void* o, const float* lse,
                             const void* dout, void* dq, void* dk, void* dv, float* delta, float* dq_acc, int B, int H,
                             int Nq, int Nk, int D, const long long* q_strides, const long long* k_strides,
                             const long long* v_strides, const long long* o_strides, const long long* do_strides,
                             const long long* dq_strides, const long long* dk_strides, const long long* dv_strides,
-                            int causal, float scale, const float* rope_cache, int rope_ctx, void* stream) {
+                            int causal, float scale, const float* rope_cache, int rope_ctx, int flags, void* stream) {
   using namespace b200;
   using namespace b200::fa2;
   B200_REQUIRE(B > 0 && H > 0 && Nq > 0 && Nk > 0, "fa2_bwd: empty problem");
@@ -457,7 +483,8 @@ extern "C" int b200_fa2_bwd_rope(const void* q, const void* k, const void* v, co
         o_strides[0], o_strides[1], o_strides[2], do_strides[0], do_strides[1], do_strides[2], rows);
     B200_LAUNCH_CHECK();
   }
-  B200_CHECK_CUDA(cudaMemsetAsync(dq_acc, 0, (size_t)rows * D * sizeof(float), s));
+  const int prezeroed = flags & 1;  // caller keeps dq_acc zero between calls; the convert pass re-zeroes it
+  if (!prezeroed) B200_CHECK_CUDA(cudaMemsetAsync(dq_acc, 0, (size_t)rows * D * sizeof(float), s));
   CUtensorMap tq, tk, tv, tdo;
   int rc;
   if ((rc = make_bhnd_map(&tq, q, B, H, Nq, D, q_strides, BM))) return rc;
@@ -473,6 +500,7 @@ extern "C" int b200_fa2_bwd_rope(const void* q, const void* k, const void* v, co
   p.scale = scale; p.scale_log2 = scale * kLog2e;
   p.num_q_tiles = ceil_div(Nq, BM);
   p.rope_cache = rope_cache; p.rope_ctx = rope_ctx;
+  p.rope_epilogue = (rope_cache != nullptr && D == 64) ? 1 : 0;
   rc = D <= 64 ? launch_bwd<64>(tq, tk, tv, tdo, p, B, s) : launch_bwd<128>(tq, tk, tv, tdo, p, B, s);
   if (rc) return rc;
   {
@@ -480,9 +508,9 @@ extern "C" int b200_fa2_bwd_rope(const void* q, const void* k, const void* v, co
     const int threads = 256;
     fa2_dq_convert_kernel<<<(unsigned)((total / 2 + threads - 1) / threads), threads, 0, s>>>(
         dq_acc, reinterpret_cast<__nv_bfloat16*>(dq), H, Nq, D, dq_strides[0], dq_strides[1], dq_strides[2], total,
-        rope_cache, rope_ctx);
+        rope_cache, rope_ctx, prezeroed);
     B200_LAUNCH_CHECK();
-    if (rope_cache != nullptr) {
+    if (rope_cache != nullptr && !p.rope_epilogue) {
       const long long pairs = (long long)B * H * Nk * (D / 2);
       fa2_dk_unrope_kernel<<<(unsigned)((pairs + threads - 1) / threads), threads, 0, s>>>(
           reinterpret_cast<__nv_bfloat16*>(dk), H, Nk, D, dk_strides[0], dk_strides[1], dk_strides[2], pairs,

@@ -27,7 +27,8 @@ int b200_device_info(int* sm_count, int* cc_major, int* cc_minor);
  *   a_mn_major = 0: A stored [M,K] row-major (lda = row stride);  1: A stored [K,M] row-major.
  *   b_mn_major = 0: B stored [N,K] row-major (ldb = row stride);  1: B stored [K,N] row-major.
  *   epilogue: 0 C bf16 = acc | 1 C fp32 = acc | 2 C fp32 += acc |
- *             3 C bf16 [M,N/2] = silu(acc[:,2j])*acc[:,2j+1] | 4 C fp32 = aux fp32 + acc
+ *             3 C bf16 [M,N/2] = silu(acc[:,2j])*acc[:,2j+1] | 4 C fp32 = aux fp32 + acc |
+ *             6 Ct fp32 [N,M] = acc transposed (ldc = row stride of Ct; both operands MN-major)
  *   force_bn: 0 = heuristic, else tile width 128/192/256.
  * ref: every Linear of the LM → cuBLAS (cs336-basics/cs336_basics/model.py:41). */
 int b200_gemm_bf16(const void* A, const void* B, void* C, const void* aux, int M, int N, int K, int lda, int ldb,
@@ -54,6 +55,16 @@ int b200_fa2_bwd(const void* q, const void* k, const void* v, const void* o, con
                  const long long* q_strides, const long long* k_strides, const long long* v_strides,
                  const long long* o_strides, const long long* do_strides, const long long* dq_strides,
                  const long long* dk_strides, const long long* dv_strides, int causal, float scale, void* stream);
+
+/* Extended form: rope_cache (nullable, fp32 (2, rope_ctx, D/2)) = q,k were rotated before attention, so dq and dk are
+ * un-rotated on the way out (fused into the fp32->bf16 pass of dq and the dK epilogue).  flags bit 0: dq_acc is
+ * already all-zero and must be left all-zero (the convert pass re-zeroes it; saves a memset per call). */
+int b200_fa2_bwd_ex(const void* q, const void* k, const void* v, const void* o, const float* lse, const void* dout,
+                    void* dq, void* dk, void* dv, float* delta, float* dq_acc, int B, int H, int Nq, int Nk, int D,
+                    const long long* q_strides, const long long* k_strides, const long long* v_strides,
+                    const long long* o_strides, const long long* do_strides, const long long* dq_strides,
+                    const long long* dk_strides, const long long* dv_strides, int causal, float scale,
+                    const float* rope_cache, int rope_ctx, int flags, void* stream);
 
 /* ---- fused normalisation / elementwise ---------------------------------------------------------
  * ref: RMSNorm model.py:101-107, residual adds model.py:380-386. */

@@ -63,6 +63,18 @@ def test_gemm_tn_wgrad(M, N, K):
     assert _rel_err(out, 2 * ref) < 2e-3
 
 
+@pytest.mark.parametrize("n_out,k_in,T", [(6400, 1600, 2048), (1600, 6400, 2048), (136, 72, 200), (72, 136, 200)])
+def test_wgrad_orientation(n_out, k_in, T):
+    """kernels.wgrad picks the wide orientation (transposed-store epilogue) for tall results."""
+    k = _k()
+    torch.manual_seed(5)
+    dy = _bf(torch.randn(T, n_out, device="cuda"))
+    x = _bf(torch.randn(T, k_in, device="cuda"))
+    out = torch.full((n_out, k_in), 3.0, device="cuda")
+    k.wgrad(dy, x, out=out)
+    assert _rel_err(out, dy.float().t() @ x.float()) < 2e-3
+
+
 def test_gemm_strided_column_slice_operand():
     """wgrad of a fused projection reads a column slice of dy (lda = full width)."""
     k = _k()
