@@ -210,43 +210,37 @@ fa2_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       const int q0 = (i_start + it) * BM;
       const int row = q0 + r;
       const bool row_ok = row < p.Nq;
-      const float L2 = row_ok ? p.lse[bh * p.Nq + row] * kLog2e : INFINITY;
+      const float L2 = row_ok ? p.lse[bh * p.Nq + row] * kLog2e : 0.f;  // rows past the end are masked through lim = 0
       const float dl = row_ok ? p.delta[bh * p.Nq + row] : 0.f;
       const bool need_mask = (kv0 + BN > p.Nk) || (p.causal && kv0 + BN - 1 > q0);
       ptx::mbar_wait(sdp_full, it & 1);
       ptx::tc_fence_after();
+      int lim = p.Nk - kv0;  // keys [kv0, kv0 + lim) are visible to this query row
+      if (p.causal) lim = min(lim, row - kv0 + 1);
+      if (!row_ok) lim = 0;
 #pragma unroll
       for (int c = 0; c < BN / 32; ++c) {
         uint32_t s[32], dp[32];
         ptx::tmem_ld_32x32b_x32(tmem_base + C::COL_S + lane_base + c * 32, s);
         ptx::tmem_ld_32x32b_x32(tmem_base + C::COL_DP + lane_base + c * 32, dp);
         ptx::tmem_ld_wait();
-        float pv[32], dsv[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float e = exp2f(fmaf(__uint_as_float(s[i]), p.scale_log2, -L2));
-          if (need_mask) {
-            const int col = kv0 + c * 32 + i;
-            const bool ok = col < p.Nk && (!p.causal || col <= row);
-            e = ok ? e : 0.f;
-          }
-          pv[i] = e;
-          dsv[i] = e * (__uint_as_float(dp[i]) - dl) * p.scale;
-        }
+        const bool whole = (!need_mask && row_ok) || lim >= (c + 1) * 32;
 #pragma unroll
         for (int v = 0; v < 4; ++v) {
-          u32x4 o;
-          o.x = pack_bf16x2(pv[8 * v + 0], pv[8 * v + 1]);
-          o.y = pack_bf16x2(pv[8 * v + 2], pv[8 * v + 3]);
-          o.z = pack_bf16x2(pv[8 * v + 4], pv[8 * v + 5]);
-          o.w = pack_bf16x2(pv[8 * v + 6], pv[8 * v + 7]);
+          float e[8], d[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) e[i] = exp2f(fmaf(__uint_as_float(s[8 * v + i]), p.scale_log2, -L2));
+          if (!whole) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) e[i] = (c * 32 + 8 * v + i < lim) ? e[i] : 0.f;
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) d[i] = e[i] * (__uint_as_float(dp[8 * v + i]) - dl) * p.scale;
           const uint32_t off = swz_off_b(r, c * 32 + v * 8, BM);
-          *reinterpret_cast<u32x4*>(sP + off) = o;
-          o.x = pack_bf16x2(dsv[8 * v + 0], dsv[8 * v + 1]);
-          o.y = pack_bf16x2(dsv[8 * v + 2], dsv[8 * v + 3]);
-          o.z = pack_bf16x2(dsv[8 * v + 4], dsv[8 * v + 5]);
-          o.w = pack_bf16x2(dsv[8 * v + 6], dsv[8 * v + 7]);
-          *reinterpret_cast<u32x4*>(sdS + off) = o;
+          *reinterpret_cast<u32x4*>(sP + off) = u32x4{pack_bf16x2(e[0], e[1]), pack_bf16x2(e[2], e[3]),
+                                                       pack_bf16x2(e[4], e[5]), pack_bf16x2(e[6], e[7])};
+          *reinterpret_cast<u32x4*>(sdS + off) = u32x4{pack_bf16x2(d[0], d[1]), pack_bf16x2(d[2], d[3]),
+                                                        pack_bf16x2(d[4], d[5]), pack_bf16x2(d[6], d[7])};
         }
       }
       ptx::tc_fence_before();

@@ -44,6 +44,7 @@ struct FwdParams {
   int causal;
   float scale_log2;  // softmax scale * log2(e)
   int num_m_tiles;
+  long long* trace;  // debug: when non-null, thread 0 of CTA (0,0,0) stores clock64() stamps of its softmax loop
 };
 
 // byte offset of element (row, col) in a K-major [rows × 128] bf16 tile made of two 64-column blocks,
@@ -184,12 +185,21 @@ fa2_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 #pragma unroll
     for (int i = 0; i < DP; ++i) o_acc[i] = 0.f;
     float m_run = -INFINITY, l_run = 0.f;
+    const bool tr = p.trace != nullptr && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
+    int tk = 0;
+#define FA_STAMP() do { if (tr && tk < 250) p.trace[tk++] = clock64(); } while (0)
+    FA_STAMP();
 
     for (int j = 0; j < n_kv; ++j) {
       const int kv0 = j * BN;
       const bool need_mask = (kv0 + BN > p.Nk) || (p.causal && kv0 + BN - 1 > m0);
       ptx::mbar_wait(s_full, j & 1);
       ptx::tc_fence_after();
+      FA_STAMP();  // S ready
+      // Per-row count of valid keys in this tile: keys [kv0, kv0 + lim) are visible to this query row
+      // (sequence end and, if causal, the diagonal).  lim >= BN: nothing to mask.
+      int lim = p.Nk - kv0;
+      if (p.causal) lim = min(lim, row - kv0 + 1);
       // ---- pass 1: row max
       float mx = -INFINITY;
 #pragma unroll
@@ -197,47 +207,41 @@ fa2_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         uint32_t s[32];
         ptx::tmem_ld_32x32b_x32(tmem_S + lane_base + c * 32, s);
         ptx::tmem_ld_wait();
-        if (need_mask) {
+        if (!need_mask || lim >= (c + 1) * 32) {  // whole chunk visible (the common case)
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const int col = kv0 + c * 32 + i;
-            const bool ok = col < p.Nk && (!p.causal || col <= row);
-            mx = fmaxf(mx, ok ? __uint_as_float(s[i]) : -INFINITY);
-          }
+          for (int i = 0; i < 32; i += 2) mx = fmaxf(mx, fmaxf(__uint_as_float(s[i]), __uint_as_float(s[i + 1])));
         } else {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(s[i]));
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, (c * 32 + i < lim) ? __uint_as_float(s[i]) : -INFINITY);
         }
       }
+      FA_STAMP();  // pass 1 done
       const float m_new = fmaxf(m_run, mx * p.scale_log2);
       const float m_use = (m_new == -INFINITY) ? 0.f : m_new;  // fully-masked row so far
       const float alpha = exp2f(m_run - m_use);                // m_run = -inf → 0
-      // ---- pass 2: P = exp2(S·scale − m), row sum, bf16 P → swizzled smem
+      // ---- pass 2: P = exp2(S·scale − m), row sum, bf16 P → swizzled smem (8 elements = one 16-byte store)
       float psum = 0.f;
 #pragma unroll
       for (int c = 0; c < BN / 32; ++c) {
         uint32_t s[32];
         ptx::tmem_ld_32x32b_x32(tmem_S + lane_base + c * 32, s);
         ptx::tmem_ld_wait();
-        float pv[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float e = exp2f(fmaf(__uint_as_float(s[i]), p.scale_log2, -m_use));
-          if (need_mask) {
-            const int col = kv0 + c * 32 + i;
-            const bool ok = col < p.Nk && (!p.causal || col <= row);
-            e = ok ? e : 0.f;
-          }
-          pv[i] = e;
-          psum += e;
-        }
+        const bool whole = !need_mask || lim >= (c + 1) * 32;
 #pragma unroll
         for (int v = 0; v < 4; ++v) {
+          float e[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) e[i] = exp2f(fmaf(__uint_as_float(s[8 * v + i]), p.scale_log2, -m_use));
+          if (!whole) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) e[i] = (c * 32 + 8 * v + i < lim) ? e[i] : 0.f;
+          }
+          psum += ((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[7]));
           u32x4 o;
-          o.x = pack_bf16x2(pv[8 * v + 0], pv[8 * v + 1]);
-          o.y = pack_bf16x2(pv[8 * v + 2], pv[8 * v + 3]);
-          o.z = pack_bf16x2(pv[8 * v + 4], pv[8 * v + 5]);
-          o.w = pack_bf16x2(pv[8 * v + 6], pv[8 * v + 7]);
+          o.x = pack_bf16x2(e[0], e[1]);
+          o.y = pack_bf16x2(e[2], e[3]);
+          o.z = pack_bf16x2(e[4], e[5]);
+          o.w = pack_bf16x2(e[6], e[7]);
           *reinterpret_cast<u32x4*>(sP + swz_off(r, c * 32 + v * 8, BM)) = o;
         }
       }
@@ -245,6 +249,7 @@ fa2_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       ptx::fence_proxy_async();    // P stores visible to the tensor core (async proxy)
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(p_full);
+      FA_STAMP();  // P published
       // ---- rescale the running row while the PV MMA runs
       l_run = l_run * alpha + psum;
       m_run = m_new;
@@ -253,6 +258,7 @@ fa2_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       // ---- accumulate the PV partial
       ptx::mbar_wait(o_full, j & 1);
       ptx::tc_fence_after();
+      FA_STAMP();  // PV ready
 #pragma unroll
       for (int c = 0; c < DP / 32; ++c) {
         uint32_t t[32];
@@ -262,6 +268,7 @@ fa2_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         for (int i = 0; i < 32; ++i) o_acc[c * 32 + i] += __uint_as_float(t[i]);
       }
       // (the next p_full arrive orders these reads before the next PV overwrite)
+      FA_STAMP();  // O accumulated
     }
 
     // ---- epilogue: O / l, logsumexp
@@ -329,6 +336,10 @@ static int launch_fwd(const CUtensorMap& q, const CUtensorMap& k, const CUtensor
 }  // namespace fa2
 }  // namespace b200
 
+static long long* g_fa2_fwd_trace = nullptr;
+// debug hook: device buffer of >= 256 int64 that receives clock64() stamps of one softmax thread (nullptr = off)
+extern "C" void b200_fa2_fwd_set_trace(long long* dev_buf) { g_fa2_fwd_trace = dev_buf; }
+
 extern "C" int b200_fa2_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int H, int Nq,
                             int Nk, int D, const long long* q_strides, const long long* k_strides,
                             const long long* v_strides, const long long* o_strides, int causal, float scale,
@@ -350,6 +361,7 @@ extern "C" int b200_fa2_fwd(const void* q, const void* k, const void* v, void* o
   p.causal = causal;
   p.scale_log2 = scale * kLog2e;
   p.num_m_tiles = ceil_div(Nq, BM);
+  p.trace = g_fa2_fwd_trace;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   return D <= 64 ? launch_fwd<64>(tq, tk, tv, p, B, s) : launch_fwd<128>(tq, tk, tv, p, B, s);
 }
