@@ -405,6 +405,14 @@ def allreduce_avg(arena, byte_off: int, numel: int, dtype: torch.dtype, one_shot
     _count()
 
 
+def bcast_pull(arena, byte_off: int, nbytes: int, src: int, signal_slot: int = 0) -> None:
+    """Every rank but ``src`` copies ``nbytes`` at ``byte_off`` of ``src``'s arena into its own (one kernel)."""
+    check(_lib().b200_bcast_pull(arena.peer_ptrs_c, arena.signal_ptrs_c, c_longlong(byte_off), c_longlong(nbytes),
+                                 c_int(src), c_int(arena.rank), c_int(arena.world_size), c_int(0),
+                                 c_int(signal_slot), stream_ptr()), "bcast_pull")
+    _count()
+
+
 def symm_barrier(arena, signal_slot: int) -> None:
     check(_lib().b200_symm_barrier(arena.signal_ptrs_c, c_int(arena.rank), c_int(arena.world_size),
                                    c_int(signal_slot), stream_ptr()), "symm_barrier")

@@ -61,6 +61,13 @@ def broadcast_parameters(module: nn.Module, src: int = 0, group=None, buffers: b
     groups: "OrderedDict[tuple, list[torch.Tensor]]" = OrderedDict()
     for t in tensors:
         groups.setdefault((t.dtype, t.device), []).append(t.data)
+    if _comm._choice(None) in ("auto", "symm"):
+        # NVLink path: one pull kernel over a packed symmetric buffer
+        from . import symm
+        ok, _ = symm.is_legal([t.device for t in tensors], [torch.float32] * len(tensors), group)
+        if ok and all(t.is_contiguous() for t in tensors):
+            symm.broadcast_tensors([t.data for t in tensors], src, group)
+            return
     for (_dtype, _dev), ts in groups.items():
         flat = torch.cat([t.reshape(-1) for t in ts])
         dist.broadcast(flat, src=src, group=group)

@@ -159,3 +159,29 @@ class SymmReducer:
         ev = torch.cuda.Event()
         ev.record(self.stream)
         torch.cuda.current_stream(self.device).wait_event(ev)
+
+
+@torch.no_grad()
+def broadcast_tensors(tensors, src: int, group=None) -> None:
+    """Make ``tensors`` (same device, any dtypes) equal to rank ``src``'s copies with ONE NVLink pull kernel over a
+    packed symmetric staging buffer (the reference issues one NCCL broadcast per parameter)."""
+    from ..ops import kernels
+
+    if not tensors:
+        return
+    dev = tensors[0].device
+    offs, off = [], 0
+    for t in tensors:
+        offs.append(off)
+        off += (t.numel() * t.element_size() + 255) // 256 * 256
+    arena = SymmArena(off, dev, group)
+    views = [arena.bytes.narrow(0, o, t.numel() * t.element_size()).view(t.dtype).view(t.shape) for o, t in zip(offs, tensors)]
+    if arena.rank == src:
+        for v, t in zip(views, tensors):
+            v.copy_(t)
+    kernels.bcast_pull(arena, 0, off, src)
+    if arena.rank != src:
+        for v, t in zip(views, tensors):
+            t.copy_(v)
+    torch.cuda.synchronize(dev)
+    dist.barrier(arena.group)

@@ -245,6 +245,29 @@ __global__ void __launch_bounds__(kThreads) allreduce_multimem_kernel(Peers P, c
 
 __global__ void barrier_kernel(Peers P, int rank, int ws, int slot) { cross_rank_barrier(P, rank, ws, slot); }
 
+// Broadcast by pull: every non-source rank copies [byte_off, byte_off + nvec32*32) of the source's arena into its
+// own over NVLink (256-bit peer loads, 4 in flight per thread).  Replaces one NCCL broadcast per parameter at DDP
+// construction (ddp_bucketed_overlapped_sharded.py:225-226,260-261) with one kernel over the packed arena.
+__global__ void __launch_bounds__(kThreads) bcast_pull_kernel(Peers P, long long byte_off, long long nvec32, int src,
+                                                              int rank, int ws, int slot) {
+  cross_rank_barrier(P, rank, ws, slot);  // the source's data is in place
+  if (rank != src) {
+    const char* from = static_cast<const char*>(P.ptr[src]) + byte_off;
+    char* to = static_cast<char*>(P.ptr[rank]) + byte_off;
+    const long long stride = (long long)gridDim.x * kThreads;
+    for (long long i0 = (long long)blockIdx.x * kThreads + threadIdx.x; i0 < nvec32; i0 += 4 * stride) {
+      v8f v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (i0 + u * stride < nvec32) v[u] = ld_peer8(from + (i0 + u * stride) * 32);
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (i0 + u * stride < nvec32) st_peer8(to + (i0 + u * stride) * 32, v[u]);
+    }
+  }
+  cross_rank_barrier(P, rank, ws, slot);  // the source may reuse its buffer
+}
+
 static int load_peers(const unsigned long long* peer_ptrs_host, const unsigned long long* signal_ptrs_host, int ws,
                       Peers* out) {
   for (int r = 0; r < kMaxRanks; ++r) {
@@ -316,6 +339,24 @@ extern "C" int b200_symm_barrier(const unsigned long long* signal_ptrs_host, int
   Peers P;
   if (int rc = load_peers(nullptr, signal_ptrs_host, world_size, &P)) return rc;
   barrier_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(P, rank, world_size, signal_slot);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200_bcast_pull(const unsigned long long* peer_ptrs_host, const unsigned long long* signal_ptrs_host,
+                               long long byte_off, long long nbytes, int src_rank, int rank, int world_size, int blocks,
+                               int signal_slot, void* stream) {
+  B200_REQUIRE(world_size >= 1 && world_size <= kMaxRanks, "bcast: world size %d unsupported", world_size);
+  B200_REQUIRE(src_rank >= 0 && src_rank < world_size, "bcast: bad source rank %d", src_rank);
+  B200_REQUIRE(byte_off % 32 == 0, "bcast: offset must be 32-byte aligned");
+  if (nbytes <= 0) return 0;
+  Peers P;
+  if (int rc = load_peers(peer_ptrs_host, signal_ptrs_host, world_size, &P)) return rc;
+  if (blocks <= 0) blocks = 48;
+  if (blocks > kMaxBlocks) blocks = kMaxBlocks;
+  bcast_pull_kernel<<<blocks, kThreads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(P, byte_off, (nbytes + 31) / 32,
+                                                                                      src_rank, rank, world_size,
+                                                                                      signal_slot);
   B200_LAUNCH_CHECK();
   return 0;
 }

@@ -146,6 +146,11 @@ int b200_comm_signal_words(void);
 int b200_allreduce(const unsigned long long* peer_ptrs_host, const unsigned long long* signal_ptrs_host,
                    void* multicast_ptr, long long byte_off, long long numel, int dtype, float scale, int rank,
                    int world_size, int algo, int blocks, int signal_slot, void* stream);
+/* Broadcast by pull over NVLink: every rank != src_rank copies nbytes at byte_off of src_rank's arena into its own.
+ * ref: one dist.broadcast(param, src=0) per parameter at DDP construction (...sharded.py:225-226,260-261). */
+int b200_bcast_pull(const unsigned long long* peer_ptrs_host, const unsigned long long* signal_ptrs_host,
+                    long long byte_off, long long nbytes, int src_rank, int rank, int world_size, int blocks,
+                    int signal_slot, void* stream);
 /* Cross-rank barrier on the signal pads (orders peer stores before what follows on every rank). */
 int b200_symm_barrier(const unsigned long long* signal_ptrs_host, int rank, int world_size, int signal_slot,
                       void* stream);

@@ -68,7 +68,7 @@ def _ddp_worker(rank, ws, port):
     from cs336_a2_systems_b200.optim import AdamW
     from cs336_a2_systems_b200.parallel import DDPBucketed, DDPIndividualParameters, ShardedOptimizer
     dev = _init(rank, ws, port)
-    torch.manual_seed(0)
+    torch.manual_seed(rank)  # replicas start different: the NVLink pull-broadcast at wrap time must equalise them
     base = TransformerLM(vocab_size=512, context_length=128, d_model=128, num_layers=2, num_heads=2, d_ff=256).to(dev)
     models = {"c10d": DDPBucketed(copy.deepcopy(base), 0.25, backend="c10d"),
               "symm": DDPBucketed(copy.deepcopy(base), 0.25, backend="symm"),
