@@ -8,6 +8,7 @@ current stream, and raise on any non-zero return code.  No autograd here — see
 from __future__ import annotations
 
 import ctypes
+from os import environ as _environ
 from ctypes import c_float, c_int, c_longlong, c_void_p
 
 import torch
@@ -20,6 +21,9 @@ BF16, F32 = 0, 1
 _DT = {torch.bfloat16: BF16, torch.float32: F32}
 
 EPI_BF16, EPI_F32, EPI_F32_ACC, EPI_BF16_SWIGLU, EPI_F32_RESID, EPI_BF16_ROPE, EPI_F32_T = 0, 1, 2, 3, 4, 5, 6
+
+#: route eligible GEMMs through the CTA-pair (cta_group::2) kernel
+GEMM_PAIR = _environ.get("B200SYS_GEMM_PAIR", "auto")  # "auto": per-shape choice, "1": always when legal, "0": never
 
 #: launch counter (kernels launched through this module), for bench.py's "gpu_launches"
 launches = 0
@@ -37,6 +41,31 @@ def _lib():
 # ------------------------------------------------------------------------------------------------
 # GEMM
 # ------------------------------------------------------------------------------------------------
+import functools as _functools
+
+
+@_functools.lru_cache(maxsize=None)
+def _plan_gemm(M: int, N: int, b_mn: bool, pair_ok: bool, sms: int = 148):
+    """Pick (use_pair, tile width) by a wave model calibrated on B200 (profiles/gemm_*): a 1-CTA tile of width BN
+    costs BN·{1.0, 1.05, 1.38} for BN = 256/192/128 (narrow tiles are issue-bound); a CTA-pair tile (256 rows)
+    costs BN·0.9 on half as many schedulable units."""
+    ceil = lambda a, b: -(-a // b)
+    nm = ceil(M, 128)
+    best = (False, 256, float("inf"))
+    for bn, pen in ((256, 1.0), (192, 1.05), (128, 1.38)):
+        cost = ceil(nm * ceil(N, bn), sms) * bn * pen
+        if cost < best[2]:
+            best = (False, bn, cost)
+    if pair_ok:
+        for bn, pen in ((256, 0.90), (192, 0.93), (128, 1.05)):
+            if b_mn and bn % 128:
+                continue
+            cost = ceil(ceil(nm, 2) * ceil(N, bn), sms // 2) * bn * pen
+            if cost < best[2]:
+                best = (True, bn, cost)
+    return best[0], best[1]
+
+
 def gemm_supported(a: Tensor, b: Tensor) -> bool:
     """TMA needs 16-byte aligned bases and row strides, unit inner stride."""
     for t in (a, b):
@@ -61,7 +90,7 @@ def wgrad(dy: Tensor, x: Tensor, out: Tensor | None = None) -> Tensor:
 
 def gemm(a: Tensor, b: Tensor, *, a_mn: bool = False, b_mn: bool = False, epilogue: int = EPI_BF16,
          out: Tensor | None = None, aux: Tensor | None = None, force_bn: int = 0,
-         rope: tuple | None = None) -> Tensor:
+         rope: tuple | None = None, pair: bool | None = None) -> Tensor:
     """``C = A · Bᵀ``.  ``a``: [M,K] (or [K,M] when ``a_mn``); ``b``: [N,K] (or [K,N] when ``b_mn``).
 
     ``rope=(cache, S, head_dim, n_cols)`` selects the RoPE epilogue: columns ``< n_cols`` of the bf16 output
@@ -86,7 +115,14 @@ def gemm(a: Tensor, b: Tensor, *, a_mn: bool = False, b_mn: bool = False, epilog
     else:
         assert tuple(out.shape) == out_shape and out.stride(1) == 1
     ld_aux = aux.stride(0) if (aux is not None and rope is None) else 0
-    check(_lib().b200_gemm_bf16_ex(p(a), p(b), p(out), p(aux), c_int(M), c_int(N), c_int(K), c_int(a.stride(0)),
+    # CTA-pair kernel (tcgen05 cta_group::2, 256-row tiles): plain / fp32 / RoPE / transposed epilogues
+    pair_ok = epilogue in (EPI_BF16, EPI_F32, EPI_BF16_ROPE, EPI_F32_T) and not (a_mn and not b_mn) and M >= 256
+    if pair is None and GEMM_PAIR == "auto" and force_bn == 0:
+        use_pair, force_bn = _plan_gemm(M, N, b_mn, pair_ok)
+    else:
+        use_pair = pair_ok and (pair if pair is not None else GEMM_PAIR == "1")
+    fn = _lib().b200_gemm2_bf16_ex if use_pair else _lib().b200_gemm_bf16_ex
+    check(fn(p(a), p(b), p(out), p(aux), c_int(M), c_int(N), c_int(K), c_int(a.stride(0)),
                                    c_int(b.stride(0)), c_int(out.stride(0)), c_int(ld_aux), c_int(int(a_mn)),
                                    c_int(int(b_mn)), c_int(epilogue), c_int(force_bn), c_int(rope_S), c_int(rope_dh),
                                    c_int(rope_cols), c_int(rope_ctx), stream_ptr()), "gemm")

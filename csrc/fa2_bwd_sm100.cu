@@ -206,12 +206,23 @@ fa2_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     const int r = warp * 32 + lane;
     const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
     const long long bh = (long long)b * p.H + h;
+    // per-row logsumexp / delta of the NEXT query tile are fetched one iteration ahead (global-load latency off
+    // the critical path)
+    float lse_next = 0.f, dl_next = 0.f;
+    if (n_iter > 0) {
+      const int row0 = i_start * BM + r;
+      if (row0 < p.Nq) { lse_next = p.lse[bh * p.Nq + row0]; dl_next = p.delta[bh * p.Nq + row0]; }
+    }
     for (int it = 0; it < n_iter; ++it) {
       const int q0 = (i_start + it) * BM;
       const int row = q0 + r;
       const bool row_ok = row < p.Nq;
-      const float L2 = row_ok ? p.lse[bh * p.Nq + row] * kLog2e : 0.f;  // rows past the end are masked through lim = 0
-      const float dl = row_ok ? p.delta[bh * p.Nq + row] : 0.f;
+      const float L2 = row_ok ? lse_next * kLog2e : 0.f;  // rows past the end are masked through lim = 0
+      const float dl = row_ok ? dl_next : 0.f;
+      if (it + 1 < n_iter && row + BM < p.Nq) {
+        lse_next = p.lse[bh * p.Nq + row + BM];
+        dl_next = p.delta[bh * p.Nq + row + BM];
+      }
       const bool need_mask = (kv0 + BN > p.Nk) || (p.causal && kv0 + BN - 1 > q0);
       ptx::mbar_wait(sdp_full, it & 1);
       ptx::tc_fence_after();
