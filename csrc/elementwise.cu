@@ -4,6 +4,7 @@
 // Reference counterparts (all chains of ATen kernels): RoPE model.py:135-147, SwiGLU pointwise
 // model.py:397,526-527, embedding model.py:57, autocast weight casts (implicit in torch.autocast).
 #include "common.cuh"
+#include "ptx.cuh"
 
 namespace b200 {
 
@@ -34,6 +35,8 @@ __global__ void rope_qk_kernel(__nv_bfloat16* __restrict__ qkv, const float* __r
 // ab: [T, 2F] bf16 with a = ab[:, :F] (gate pre-activation), b = ab[:, F:] (up); g = silu(a) * b
 __global__ void swiglu_fwd_kernel(const __nv_bfloat16* __restrict__ ab, __nv_bfloat16* __restrict__ g, int F,
                                   size_t total_vec /* T*F/8 */) {
+  ptx::griddep_launch();
+  ptx::griddep_wait();
   const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= total_vec) return;
   const int fv = F / 8;
@@ -54,6 +57,8 @@ __global__ void swiglu_fwd_kernel(const __nv_bfloat16* __restrict__ ab, __nv_bfl
 // dab[:, :F] = dg * b * (sig + a*sig*(1-sig)),  dab[:, F:] = dg * a * sig
 __global__ void swiglu_bwd_kernel(const __nv_bfloat16* __restrict__ ab, const __nv_bfloat16* __restrict__ dg,
                                   __nv_bfloat16* __restrict__ dab, int F, size_t total_vec) {
+  ptx::griddep_launch();
+  ptx::griddep_wait();
   const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= total_vec) return;
   const int fv = F / 8;
@@ -131,9 +136,9 @@ extern "C" int b200_swiglu_fwd(const void* ab, void* g, long long T, int F, void
   B200_REQUIRE(F % 8 == 0, "swiglu: d_ff must be a multiple of 8");
   const size_t total = (size_t)T * F / 8;
   if (total == 0) return 0;
-  swiglu_fwd_kernel<<<(unsigned)((total + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const __nv_bfloat16*>(ab), reinterpret_cast<__nv_bfloat16*>(g), F, total);
-  B200_LAUNCH_CHECK();
+  B200_CHECK_CUDA(launch_pdl(swiglu_fwd_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0,
+                             reinterpret_cast<cudaStream_t>(stream), reinterpret_cast<const __nv_bfloat16*>(ab),
+                             reinterpret_cast<__nv_bfloat16*>(g), F, total));
   return 0;
 }
 
@@ -141,10 +146,9 @@ extern "C" int b200_swiglu_bwd(const void* ab, const void* dg, void* dab, long l
   B200_REQUIRE(F % 8 == 0, "swiglu: d_ff must be a multiple of 8");
   const size_t total = (size_t)T * F / 8;
   if (total == 0) return 0;
-  swiglu_bwd_kernel<<<(unsigned)((total + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const __nv_bfloat16*>(ab), reinterpret_cast<const __nv_bfloat16*>(dg),
-      reinterpret_cast<__nv_bfloat16*>(dab), F, total);
-  B200_LAUNCH_CHECK();
+  B200_CHECK_CUDA(launch_pdl(swiglu_bwd_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0,
+                             reinterpret_cast<cudaStream_t>(stream), reinterpret_cast<const __nv_bfloat16*>(ab),
+                             reinterpret_cast<const __nv_bfloat16*>(dg), reinterpret_cast<__nv_bfloat16*>(dab), F, total));
   return 0;
 }
 

@@ -109,10 +109,12 @@ fa2_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     ptx::tmem_alloc(tmem_slot, C::TMEM_COLS);
     ptx::tmem_relinquish();
   }
+  ptx::griddep_launch();
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  ptx::griddep_wait();
 
   if (warp == 4) {
     // ===================================== TMA producer =====================================
@@ -369,6 +371,8 @@ fa2_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 __global__ void fa2_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ dout,
                                  float* __restrict__ delta, int H, int Nq, int D, long long o_sb, long long o_sh,
                                  long long o_sr, long long d_sb, long long d_sh, long long d_sr, long long rows) {
+  ptx::griddep_launch();
+  ptx::griddep_wait();
   const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (w >= rows) return;
@@ -391,6 +395,8 @@ __global__ void fa2_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv
 __global__ void fa2_dq_convert_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dq, int H, int Nq,
                                       int D, long long sb, long long sh, long long sr, long long total,
                                       const float* __restrict__ rope_cache, int rope_ctx, int rezero) {
+  ptx::griddep_launch();
+  ptx::griddep_wait();
   const long long idx = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 2;
   if (idx >= total) return;
   const int d = (int)(idx % D);
@@ -441,8 +447,7 @@ static int launch_bwd(const CUtensorMap& q, const CUtensorMap& k, const CUtensor
     configured = true;
   }
   dim3 grid(ceil_div(p.Nk, BN), p.H, B);
-  kern<<<grid, kThreads, C::SMEM_BYTES, s>>>(q, k, v, dO, p);
-  B200_LAUNCH_CHECK();
+  B200_CHECK_CUDA(launch_pdl(kern, grid, dim3(kThreads), C::SMEM_BYTES, s, q, k, v, dO, p));
   return 0;
 }
 
@@ -483,10 +488,10 @@ extern "C" int b200_fa2_bwd_ex(const void* q, const void* k, const void* v, cons
   {
     const int threads = 256;
     const long long blocks = (rows * 32 + threads - 1) / threads;
-    fa2_delta_kernel<<<(unsigned)blocks, threads, 0, s>>>(
-        reinterpret_cast<const __nv_bfloat16*>(o), reinterpret_cast<const __nv_bfloat16*>(dout), delta, H, Nq, D,
-        o_strides[0], o_strides[1], o_strides[2], do_strides[0], do_strides[1], do_strides[2], rows);
-    B200_LAUNCH_CHECK();
+    B200_CHECK_CUDA(launch_pdl(fa2_delta_kernel, dim3((unsigned)blocks), dim3(threads), 0, s,
+                               reinterpret_cast<const __nv_bfloat16*>(o), reinterpret_cast<const __nv_bfloat16*>(dout),
+                               delta, H, Nq, D, o_strides[0], o_strides[1], o_strides[2], do_strides[0], do_strides[1],
+                               do_strides[2], rows));
   }
   const int prezeroed = flags & 1;  // caller keeps dq_acc zero between calls; the convert pass re-zeroes it
   if (!prezeroed) B200_CHECK_CUDA(cudaMemsetAsync(dq_acc, 0, (size_t)rows * D * sizeof(float), s));
@@ -511,10 +516,9 @@ extern "C" int b200_fa2_bwd_ex(const void* q, const void* k, const void* v, cons
   {
     const long long total = rows * D;
     const int threads = 256;
-    fa2_dq_convert_kernel<<<(unsigned)((total / 2 + threads - 1) / threads), threads, 0, s>>>(
-        dq_acc, reinterpret_cast<__nv_bfloat16*>(dq), H, Nq, D, dq_strides[0], dq_strides[1], dq_strides[2], total,
-        rope_cache, rope_ctx, prezeroed);
-    B200_LAUNCH_CHECK();
+    B200_CHECK_CUDA(launch_pdl(fa2_dq_convert_kernel, dim3((unsigned)((total / 2 + threads - 1) / threads)),
+                               dim3(threads), 0, s, (const float*)dq_acc, reinterpret_cast<__nv_bfloat16*>(dq), H, Nq, D,
+                               dq_strides[0], dq_strides[1], dq_strides[2], total, rope_cache, rope_ctx, prezeroed));
     if (rope_cache != nullptr && !p.rope_epilogue) {
       const long long pairs = (long long)B * H * Nk * (D / 2);
       fa2_dk_unrope_kernel<<<(unsigned)((pairs + threads - 1) / threads), threads, 0, s>>>(

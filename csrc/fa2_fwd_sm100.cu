@@ -103,10 +103,12 @@ fa2_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     ptx::tmem_alloc(tmem_slot, C::TMEM_COLS);
     ptx::tmem_relinquish();
   }
+  ptx::griddep_launch();
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  ptx::griddep_wait();
   const uint32_t tmem_S = tmem_base;
   const uint32_t tmem_O = tmem_base + BN;
 
@@ -328,8 +330,7 @@ static int launch_fwd(const CUtensorMap& q, const CUtensorMap& k, const CUtensor
     configured = true;
   }
   dim3 grid(p.num_m_tiles, p.H, B);
-  kern<<<grid, kThreads, C::SMEM_BYTES, s>>>(q, k, v, p);
-  B200_LAUNCH_CHECK();
+  B200_CHECK_CUDA(launch_pdl(kern, grid, dim3(kThreads), C::SMEM_BYTES, s, q, k, v, p));
   return 0;
 }
 

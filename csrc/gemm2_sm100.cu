@@ -72,11 +72,13 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     ptx::tmem_alloc_cg2(tmem_slot, kTmemCols2);
     ptx::tmem_relinquish_cg2();
   }
+  ptx::griddep_launch();
   ptx::tc_fence_before();
   __syncthreads();
   ptx::cluster_sync();  // both CTAs' barriers are initialised and both halves of tensor memory are allocated
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  ptx::griddep_wait();
 
   const int num_m2 = (p.num_m + 1) / 2;  // 256-row tile pairs along M
   const int total_tiles = num_m2 * p.num_n;
@@ -216,8 +218,7 @@ static int launch2(const CUtensorMap& tmA, const CUtensorMap& tmB, const Params&
   const int tiles = ceil_div(p.num_m, 2) * p.num_n;
   const int clusters = num_sms() / 2;
   const int grid = 2 * (tiles < clusters ? tiles : clusters);
-  kern<<<grid, kThreads2, C::SMEM_BYTES, stream>>>(tmA, tmB, p);
-  B200_LAUNCH_CHECK();
+  B200_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kThreads2), C::SMEM_BYTES, stream, tmA, tmB, p));
   return 0;
 }
 

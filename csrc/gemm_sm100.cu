@@ -74,10 +74,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     ptx::tmem_alloc(tmem_slot, kTmemCols);
     ptx::tmem_relinquish();
   }
+  ptx::griddep_launch();
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  ptx::griddep_wait();  // operands come from the previous kernel; everything above overlapped its tail
 
   const int total_tiles = p.num_m * p.num_n;
 
@@ -212,8 +214,7 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Params& 
   }
   const int tiles = p.num_m * p.num_n;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  kern<<<grid, kThreads, C::SMEM_BYTES, stream>>>(tmA, tmB, p);
-  B200_LAUNCH_CHECK();
+  B200_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kThreads), C::SMEM_BYTES, stream, tmA, tmB, p));
   return 0;
 }
 

@@ -5,6 +5,7 @@
 // branch output that still has to be added), writes the updated fp32 stream, the normalised bf16
 // activations for the next GEMM and the per-row rstd.  fp32 math throughout.
 #include "common.cuh"
+#include "ptx.cuh"
 
 #include <algorithm>
 #include <mutex>
@@ -31,6 +32,8 @@ __global__ void __launch_bounds__(256) rmsnorm_fwd_kernel(const TX* __restrict__
                                                           int d, float eps) {
   extern __shared__ float row[];
   __shared__ float red[32];
+  ptx::griddep_launch();
+  ptx::griddep_wait();
   const size_t base = (size_t)blockIdx.x * d;
   float ss = 0.f;
   if (sizeof(TX) == 4 && (d & 3) == 0) {
@@ -148,6 +151,8 @@ __global__ void __launch_bounds__(128) rmsnorm_bwd_dx_kernel(const TDY* __restri
                                                              const float* __restrict__ dres_in, float* __restrict__ dx,
                                                              __nv_bfloat16* __restrict__ dx_bf16, int T, int d) {
   __shared__ float red[32];
+  ptx::griddep_launch();
+  ptx::griddep_wait();
   const int r = blockIdx.x;
   const int nvec = d >> 2;
   const size_t base = (size_t)r * d;
@@ -192,6 +197,8 @@ template <typename TDY>
 __global__ void __launch_bounds__(128) rmsnorm_bwd_dw_kernel(const TDY* __restrict__ dy, const float* __restrict__ x,
                                                              const float* __restrict__ rstd, float* __restrict__ partial,
                                                              int T, int d, int rows_per_chunk) {
+  ptx::griddep_launch();
+  ptx::griddep_wait();
   const int c = blockIdx.x * 128 + threadIdx.x;  // float4 column
   if (c >= (d >> 2)) return;
   const int r0 = blockIdx.y * rows_per_chunk;
@@ -212,6 +219,8 @@ __global__ void __launch_bounds__(128) rmsnorm_bwd_dw_kernel(const TDY* __restri
 __global__ void __launch_bounds__(256) colsum4_kernel(const float* __restrict__ partial, float* __restrict__ out,
                                                       int rows, int d, int accumulate) {
   __shared__ float red[4][64];
+  ptx::griddep_launch();
+  ptx::griddep_wait();
   const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
   const int j = blockIdx.x * 64 + tx;
   float s = 0.f;
@@ -264,8 +273,9 @@ extern "C" int b200_rmsnorm_fwd(const void* x, int x_dtype, const void* resid_bf
   do {                                                                                                            \
     auto k = rmsnorm_fwd_kernel<TX, TY>;                                                                          \
     if (smem > 48 * 1024) B200_CHECK_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    k<<<T, threads, smem, s>>>(reinterpret_cast<const TX*>(x), reinterpret_cast<const __nv_bfloat16*>(resid_bf16), w, \
-                               reinterpret_cast<TY*>(y), xout, rstd, d, eps);                                     \
+    B200_CHECK_CUDA(launch_pdl(k, dim3(T), dim3(threads), smem, s, reinterpret_cast<const TX*>(x),                   \
+                               reinterpret_cast<const __nv_bfloat16*>(resid_bf16), w, reinterpret_cast<TY*>(y), xout,  \
+                               rstd, d, eps));                                                                     \
   } while (0)
   if (x_dtype == B200_F32 && y_dtype == B200_BF16) LAUNCH(float, __nv_bfloat16);
   else if (x_dtype == B200_F32 && y_dtype == B200_F32) LAUNCH(float, float);
@@ -300,8 +310,8 @@ extern "C" int b200_rmsnorm_bwd(const void* dy, int dy_dtype, const float* x, co
     const int chunks = ceil_div(T, rows_per_chunk);
     const int fgrid = chunks;
 #define LAUNCH_W(TDY, VPL)                                                                                        \
-  rmsnorm_bwd_dx_kernel<TDY, VPL><<<T, 128, 0, s>>>(reinterpret_cast<const TDY*>(dy), x, w, rstd,       \
-                                                                 dres_in, dx, dxb, T, d)
+  B200_CHECK_CUDA(launch_pdl(rmsnorm_bwd_dx_kernel<TDY, VPL>, dim3(T), dim3(128), 0, s,                            \
+                             reinterpret_cast<const TDY*>(dy), x, w, rstd, dres_in, dx, dxb, T, d))
 #define BY_DT_W(VPL)                                                   \
   do {                                                                 \
     if (dy_dtype == B200_BF16) LAUNCH_W(__nv_bfloat16, VPL);           \
@@ -316,13 +326,14 @@ extern "C" int b200_rmsnorm_bwd(const void* dy, int dy_dtype, const float* x, co
     {
       dim3 g2(ceil_div(d >> 2, 128), chunks);
       if (dy_dtype == B200_BF16)
-        rmsnorm_bwd_dw_kernel<__nv_bfloat16><<<g2, 128, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(dy), x, rstd, scratch, T, d, rows_per_chunk);
+        B200_CHECK_CUDA(launch_pdl(rmsnorm_bwd_dw_kernel<__nv_bfloat16>, g2, dim3(128), 0, s,
+                                   reinterpret_cast<const __nv_bfloat16*>(dy), x, (const float*)rstd, scratch, T, d, rows_per_chunk));
       else
-        rmsnorm_bwd_dw_kernel<float><<<g2, 128, 0, s>>>(reinterpret_cast<const float*>(dy), x, rstd, scratch, T, d, rows_per_chunk);
-      B200_LAUNCH_CHECK();
+        B200_CHECK_CUDA(launch_pdl(rmsnorm_bwd_dw_kernel<float>, g2, dim3(128), 0, s, reinterpret_cast<const float*>(dy), x,
+                                   (const float*)rstd, scratch, T, d, rows_per_chunk));
     }
-    colsum4_kernel<<<ceil_div(d, 64), 256, 0, s>>>(scratch, dw, fgrid, d, dw_accumulate);
-    B200_LAUNCH_CHECK();
+    B200_CHECK_CUDA(launch_pdl(colsum4_kernel, dim3(ceil_div(d, 64)), dim3(256), 0, s, (const float*)scratch, dw, fgrid, d,
+                               dw_accumulate));
     return 0;
   }
 #define LAUNCH(TDY, VPT, THREADS)                                                                              \

@@ -60,6 +60,13 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// ---- programmatic dependent launch ------------------------------------------------------------------
+// launch_dependents: the next kernel in the stream may start being scheduled (its prologue overlaps our tail);
+// wait: blocks until the preceding kernel has completed and its memory is visible — every kernel calls it before
+// touching global memory, so only set-up work (barrier init, TMEM allocation, descriptor prefetch) ever overlaps.
+__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---- thread-block clusters / CTA pairs -----------------------------------------------------------------
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
