@@ -123,10 +123,12 @@ def build_ours(args, rank, ws, dev):
     if args.sharded and ws > 1:
         from cs336_a2_systems_b200.parallel import ShardedOptimizer
         opt = ShardedOptimizer(model.parameters(), AdamW, **kw)
-        fused_sharded = opt.enable_symmetric()
+        fused_sharded = opt.enable_symmetric(model)
     else:
         opt = AdamW(model.parameters(), **kw)
-    trainer = Trainer(model, opt, autocast=True, cuda_graph=not args.no_graph and not (args.sharded and ws > 1),
+    bucket_fused = hasattr(getattr(opt, "_symm", None), "_reduce_bucket")
+    trainer = Trainer(model, opt, autocast=True,
+                      cuda_graph=not args.no_graph and (bucket_fused or not (args.sharded and ws > 1)),
                       overlap_optimizer=not args.no_overlap and not args.sharded)
     state = {"launches_per_step": 0}
 
@@ -143,6 +145,7 @@ def build_ours(args, rank, ws, dev):
 
     extra = {"cuda_graph": trainer.cuda_graph, "optimizer_overlapped_with_backward": trainer._overlap is not None,
              "sharded_optimizer": bool(args.sharded and ws > 1), "fused_nvlink_sharded_adamw": fused_sharded,
+             "bucket_fused_reduce_scatter_adamw_allgather": bucket_fused,
              "comm": getattr(getattr(model, "_reducer", None), "kind", "none")}
     return step_device, step_e2e, count_launches, state, extra
 

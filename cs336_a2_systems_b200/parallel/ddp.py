@@ -207,6 +207,7 @@ class DDPBucketed(_DDPBase):
         self._reducer = None
         self._pending: list = []
         self._bucket_callback = None
+        self._reduce_override = None
         if self.world_size > 1:
             self._reducer = _comm.make_reducer([b.numel for b in self.buckets], self.process_group, backend,
                                                per_parameter=False,
@@ -248,11 +249,17 @@ class DDPBucketed(_DDPBase):
         b = self.buckets[bi]
         b.launched = True
         with nvtx.range(f"ddp.allreduce_bucket{bi}"):
-            handle = self._reducer.reduce_bucket_async(bi)
+            handle = self._reduce_override(bi) if self._reduce_override is not None else \
+                self._reducer.reduce_bucket_async(bi)
             self._pending.append(handle)
         if self._bucket_callback is not None:
             # chain work behind this bucket's reduction (e.g. the optimizer update of exactly these parameters)
             self._bucket_callback(bi, b.params, self._reducer.stream_after(handle))
+
+    def set_bucket_reduce_override(self, fn) -> None:
+        """``fn(bucket_index)`` replaces the bucket all-reduce (used by the bucket-fused sharded optimizer, whose
+        kernel reduces, updates and redistributes in one go on the reducer's stream)."""
+        self._reduce_override = fn
 
     def set_bucket_callback(self, fn) -> None:
         """``fn(bucket_index, params, stream)`` is called right after a bucket's reduction has been enqueued;

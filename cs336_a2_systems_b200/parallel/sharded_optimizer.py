@@ -133,6 +133,15 @@ class ShardedOptimizer(torch.optim.Optimizer):
         Returns False (and changes nothing) when the path is not legal for this setup."""
         from . import symm_optimizer
 
+        red = getattr(module, "_reducer", None)
+        mode = symm_optimizer._mode_of(self.optimizer_cls)
+        if module is not None and hasattr(module, "buckets") and getattr(red, "kind", "") == "symm" and \
+                mode is not None and self.world_size > 1 and len(self.param_groups) == 1:
+            # DDPBucketed on the NVLink backend: fuse reduce-scatter + sharded AdamW + all-gather per bucket
+            from .zero import BucketFusedAdamW
+
+            self._symm = BucketFusedAdamW(self, module, mode)
+            return True
         s = symm_optimizer.try_make(self, module)
         self._symm = s
         return s is not None
@@ -143,6 +152,9 @@ class ShardedOptimizer(torch.optim.Optimizer):
 
     def consolidated_state_dict(self, dst: int = 0) -> dict | None:
         """Gather ``{param_index: state}`` for all parameters on ``dst`` (None elsewhere)."""
+        if hasattr(self._symm, "full_state"):
+            st = self._symm.full_state()  # collective
+            return {"state": st, "owners": {}} if self.rank == dst else None
         index = {}
         i = 0
         for g in self.param_groups:

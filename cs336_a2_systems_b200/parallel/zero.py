@@ -1,0 +1,165 @@
+"""Bucket-fused ZeRO-1 step over NVLink: gradient reduce-scatter + sharded AdamW + parameter all-gather in ONE
+kernel per DDP bucket (``csrc/comm_adamw.cu: zero_adamw_kernel``).
+
+What the reference does per step with ``DDP_Bucketed`` + ``ShardedStateOptimizer``
+(``ddp_bucketed_overlapped_sharded.py:289-318,335-340``): flatten + NCCL all-reduce of every bucket, unflatten and
+divide, the owner's AdamW over whole parameters, then one blocking NCCL broadcast per parameter tensor.
+
+Here the gradient buckets, the parameters and their bf16 GEMM shadows live in three symmetric arenas with the SAME
+element layout.  When a bucket's last gradient has been produced, one kernel on the communication stream lets
+rank r (a) average slice r of the bucket straight out of every rank's gradient arena, (b) apply AdamW with its
+slice of m and v — optimizer state and optimizer HBM traffic are 1/world_size per rank — and (c) store the new
+fp32 parameters and bf16 shadows into every rank's arenas.  ``step()`` only joins the stream.
+
+Consequences: ``param.grad`` keeps the LOCAL (unreduced) gradient after the step, and optimizer state is sharded
+by bucket slice, not by parameter (``consolidated_state_dict`` reassembles per-parameter ``m``/``v``).
+"""
+
+from __future__ import annotations
+
+import ctypes
+import os
+
+import torch
+import torch.distributed as dist
+
+from .. import _native
+from ..ops import kernels, native
+from . import symm
+
+
+class BucketFusedAdamW:
+    def __init__(self, sharded, ddp, mode: int):
+        red = ddp._reducer
+        self.sharded, self.ddp, self.mode = sharded, ddp, mode
+        self.garena = red.arena
+        self.rank, self.ws = self.garena.rank, self.garena.world_size
+        dev = red.device
+        group = red.group
+        self.device = dev
+        nbytes = self.garena.nbytes
+        self.parena = symm.SymmArena(nbytes, dev, group)
+        self.sarena = symm.SymmArena(nbytes // 2, dev, group)
+        self._off_of: dict[int, int] = {}
+        self._buckets = []
+        with torch.no_grad():
+            for bi, b in enumerate(ddp.buckets):
+                assert b.dtype == torch.float32, "bucket-fused AdamW needs fp32 parameters"
+                boff = red._offs[bi]
+                for p, off in zip(b.params, b.offsets):
+                    byte = boff + off * 4
+                    view = self.parena.view(byte, p.numel(), torch.float32).view(p.shape)
+                    view.copy_(p.data)
+                    p.data = view
+                    self._off_of[id(p)] = byte
+                nvec = (b.numel * 4 + 31) // 32
+                per = (nvec + self.ws - 1) // self.ws
+                m = torch.zeros(per * 8, dtype=torch.float32, device=dev)
+                v = torch.zeros(per * 8, dtype=torch.float32, device=dev)
+                self._buckets.append((boff, b.numel, m, v, per))
+        self._params = [p for b in ddp.buckets for p in b.params]
+        native.drop_shadows(self._params)
+        native.set_shadow_provider(self._provide_shadow)
+        probe = torch.nn.Parameter(torch.zeros(1))
+        self._defaults = dict(sharded.optimizer_cls([probe], **sharded.optimizer_kwargs).defaults)
+        # NVLS (reduce in the switch, replicate stores in the switch) pays from 3 ranks up; 2 ranks use plain P2P
+        mcs = [self.garena.multicast_ptr, self.parena.multicast_ptr, self.sarena.multicast_ptr]
+        use_mc = self.ws > 2 and all(mcs) and os.environ.get("B200SYS_MULTIMEM", "1") != "0"
+        self._mc = kernels.host_ptr_array(mcs) if use_mc else None
+        self.nvls = use_mc
+        self.hyper = torch.zeros(8, dtype=torch.float32, device=dev)
+        self._hyper_host = torch.zeros(16, 8, dtype=torch.float32).pin_memory()
+        self._hyper_slot = 0
+        self._hyper_vals = None
+        self.step_dev = torch.ones(1, dtype=torch.int32, device=dev)
+        self.t = 1
+        self._launched = False
+        ddp.set_bucket_reduce_override(self._reduce_bucket)
+        torch.cuda.synchronize(dev)
+        dist.barrier(group)
+
+    # bf16 shadow of a group of weights that are adjacent in the parameter arena = a view of the shadow arena
+    def _provide_shadow(self, weights):
+        offs = [self._off_of.get(id(w)) for w in weights]
+        if any(o is None for o in offs):
+            return None
+        for w, o, nxt in zip(weights, offs, offs[1:] + [None]):
+            if nxt is not None and o + w.numel() * 4 != nxt:
+                return None
+        rows = sum(w.shape[0] for w in weights)
+        return self.sarena.view(offs[0] // 2, rows * weights[0].shape[1], torch.bfloat16).view(rows, weights[0].shape[1])
+
+    def _set_hyper(self):
+        g = dict(self._defaults)
+        g.update({k: v for k, v in self.sharded.param_groups[0].items() if k != "params"})  # LR schedules write here
+        b1, b2 = g["betas"]
+        vals = (float(g["lr"]), float(b1), float(b2), float(g["eps"]), float(g["weight_decay"]), 1.0)
+        if vals != self._hyper_vals:
+            self._hyper_vals = vals
+            row = self._hyper_host[self._hyper_slot]
+            self._hyper_slot = (self._hyper_slot + 1) % self._hyper_host.shape[0]
+            row[:6] = torch.tensor(vals)
+            self.hyper.copy_(row, non_blocking=True)
+
+    def _reduce_bucket(self, bi: int):
+        """Called by DDPBucketed in place of its all-reduce when bucket ``bi`` is complete."""
+        red = self.ddp._reducer
+        cur = torch.cuda.current_stream(self.device)
+        if not self._launched:
+            self._set_hyper()  # on the compute stream, ordered before the event below
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        red.stream.wait_event(ev)
+        boff, numel, m, v, _per = self._buckets[bi]
+        with torch.cuda.stream(red.stream):
+            _native.check(_native.lib().b200_zero_adamw_bucket(
+                self.garena.peer_ptrs_c, self.parena.peer_ptrs_c, self.sarena.peer_ptrs_c, self.garena.signal_ptrs_c,
+                self._mc, ctypes.c_longlong(boff), ctypes.c_longlong(numel), _native.p(m), _native.p(v), _native.p(self.hyper),
+                _native.p(self.step_dev), ctypes.c_int(self.mode), ctypes.c_int(self.rank), ctypes.c_int(self.ws),
+                ctypes.c_int(0), ctypes.c_int(0), ctypes.c_void_p(red.stream.cuda_stream)), "zero_adamw_bucket")
+            kernels._count()
+        self._launched = True
+        return bi
+
+    @torch.no_grad()
+    def step(self, sharded):
+        red = self.ddp._reducer
+        if self._launched:
+            with torch.cuda.stream(red.stream):
+                _native.check(_native.lib().b200_incr_step(_native.p(self.step_dev),
+                                                           ctypes.c_void_p(red.stream.cuda_stream)), "incr_step")
+            ev = torch.cuda.Event()
+            ev.record(red.stream)
+            torch.cuda.current_stream(self.device).wait_event(ev)
+            self.t += 1
+            self._launched = False
+            # shadows that could not live in the arena (a fused group straddling a bucket edge) are re-cast lazily
+            lo = self.sarena.bytes.data_ptr()
+            hi = lo + self.sarena.nbytes
+            for p in self._params:
+                for ent, i in getattr(p, "_b200_shadow_slices", ()):
+                    if not (lo <= ent.tensor.data_ptr() < hi):
+                        ent.versions[i] = None
+
+    # ------------------------------------------------------------------ state for checkpoints
+    def full_state(self):
+        """``{param_index: {"m", "v", "t"}}`` reassembled from the bucket slices (collective)."""
+        out = {}
+        index = {}
+        i = 0
+        t = int(self.step_dev.item())  # device-resident: stays right under CUDA-graph replay
+        for g in self.sharded.param_groups:
+            for p in g["params"]:
+                index[id(p)] = i
+                i += 1
+        for bi, b in enumerate(self.ddp.buckets):
+            _boff, numel, m, v, per = self._buckets[bi]
+            full_m = torch.empty(per * 8 * self.ws, device=self.device)
+            full_v = torch.empty(per * 8 * self.ws, device=self.device)
+            dist.all_gather_into_tensor(full_m, m, group=self.garena.group)
+            dist.all_gather_into_tensor(full_v, v, group=self.garena.group)
+            for p, off in zip(b.params, b.offsets):
+                if id(p) in index:
+                    out[index[id(p)]] = {"m": full_m[off:off + p.numel()].view(p.shape).cpu(),
+                                         "v": full_v[off:off + p.numel()].view(p.shape).cpu(), "t": t}
+        return out

@@ -124,6 +124,9 @@ class Trainer:
             # torch.distributed collectives inside a captured step are not supported by this trainer (the NCCL
             # path hung under capture on B200); the NVLink backend's kernels are plain launches and capture fine
             self.cuda_graph = False
+        if max_grad_norm is not None and hasattr(getattr(optimizer, "_symm", None), "_reduce_bucket"):
+            raise ValueError("the bucket-fused sharded AdamW applies the update as each bucket's gradients arrive; "
+                             "it cannot be combined with global gradient-norm clipping")
         self.arena = None
         if grad_arena or (grad_arena is None and self.device.type == "cuda" and not self._is_ddp):
             self.arena = GradArena(list(model.parameters()))

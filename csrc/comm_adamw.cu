@@ -96,7 +96,227 @@ __global__ void incr_step_kernel_d(int* step) { *step += 1; }
 }  // namespace comm
 }  // namespace b200
 
+namespace b200 {
+namespace comm {
+
+// ------------------------------------------------------------------------------------------------
+// Fused gradient reduce-scatter + sharded AdamW + parameter all-gather for one DDP bucket.
+//
+// Gradient bucket, parameter bucket and bf16 shadow bucket have the same element layout on every rank
+// (symmetric arenas).  Rank r owns the r-th slice of the bucket: it averages that slice of the gradients
+// straight out of every rank's bucket (NVLink loads), applies AdamW with ITS slice of m and v (optimizer state
+// exists once across the job), and stores the new parameters (fp32) and their bf16 GEMM shadows into every
+// rank's arenas (NVLink stores).  One kernel replaces: all-reduce + 1/ws scale + full-model AdamW on every
+// rank + (for the reference's sharded optimizer) one broadcast per parameter.
+// ------------------------------------------------------------------------------------------------
+struct v8 { float f[8]; };
+__device__ __forceinline__ v8 ldsys8(const void* p) {
+  v8 r;
+  asm volatile("ld.global.relaxed.sys.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(r.f[0]), "=f"(r.f[1]), "=f"(r.f[2]), "=f"(r.f[3]), "=f"(r.f[4]), "=f"(r.f[5]), "=f"(r.f[6]), "=f"(r.f[7])
+               : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ void stsys8(void* p, const v8& r) {
+  asm volatile("st.global.relaxed.sys.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(r.f[0]), "f"(r.f[1]),
+               "f"(r.f[2]), "f"(r.f[3]), "f"(r.f[4]), "f"(r.f[5]), "f"(r.f[6]), "f"(r.f[7]) : "memory");
+}
+__device__ __forceinline__ void stsys4u(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.global.relaxed.sys.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ unsigned cas_rel(unsigned* a, unsigned c, unsigned v) {
+  unsigned o;
+  asm volatile("atom.global.release.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(o) : "l"(a), "r"(c), "r"(v) : "memory");
+  return o;
+}
+__device__ __forceinline__ unsigned cas_acq(unsigned* a, unsigned c, unsigned v) {
+  unsigned o;
+  asm volatile("atom.global.acquire.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(o) : "l"(a), "r"(c), "r"(v) : "memory");
+  return o;
+}
+struct ZPeers {
+  char* grad[kMaxRanksD];
+  char* param[kMaxRanksD];
+  char* shadow[kMaxRanksD];
+  unsigned int* sig[kMaxRanksD];
+};
+__device__ __forceinline__ void zbarrier(const ZPeers& P, int rank, int ws, int slot) {
+  __syncthreads();
+  if (threadIdx.x < ws) {
+    const int peer = threadIdx.x;
+    unsigned* send = P.sig[peer] + slot + blockIdx.x * kMaxRanksD + rank;
+    unsigned* recv = P.sig[rank] + slot + blockIdx.x * kMaxRanksD + peer;
+    while (cas_rel(send, 0u, 1u) != 0u) {
+    }
+    while (cas_acq(recv, 1u, 0u) != 1u) {
+    }
+  }
+  __syncthreads();
+}
+
+struct ZMulticast {
+  char* grad;    // NVLS multicast address of the gradient arena (nullptr: peer-to-peer path)
+  char* param;
+  char* shadow;
+};
+__device__ __forceinline__ void mm_ld_reduce8(const char* a, v8& r) {
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.f[0]), "=f"(r.f[1]), "=f"(r.f[2]), "=f"(r.f[3]) : "l"(a) : "memory");
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.f[4]), "=f"(r.f[5]), "=f"(r.f[6]), "=f"(r.f[7]) : "l"(a + 16) : "memory");
+}
+__device__ __forceinline__ void mm_st4(char* a, float x, float y, float z, float w) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(a), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
+
+constexpr int kZThreads = 256;
+constexpr int kZMaxBlocks = 148;  // one CTA per SM, co-resident with the backward GEMMs (<=112 regs x 256 threads next to the GEMM CTA)
+
+// WS > 0: peer-to-peer loads/stores over WS ranks.  WS == 0: NVLS — the switch reduces the gradient slice
+// (multimem.ld_reduce) and replicates the parameter / shadow stores (multimem.st).
+template <int WS>
+__global__ void __launch_bounds__(kZThreads) zero_adamw_kernel(ZPeers P, ZMulticast MC, long long byte_off,
+                                                               long long nvec32, float* __restrict__ m_slice,
+                                                               float* __restrict__ v_slice,
+                                                               const float* __restrict__ hyper,
+                                                               const int* __restrict__ step, int mode, int rank, int ws,
+                                                               int slot) {
+  constexpr int U = 2;  // vectors per thread per trip: all remote loads of a trip are in flight together
+  zbarrier(P, rank, ws, slot);  // every rank's gradients for this bucket are final
+  const float lr = hyper[0], b1 = hyper[1], b2 = hyper[2], eps = hyper[3], wd = hyper[4];
+  const float t = (float)(*step);
+  const float bc1 = 1.f - powf(b1, t), bc2 = 1.f - powf(b2, t);
+  const float alpha_t = lr * sqrtf(bc2) / bc1, rsqrt_bc2 = rsqrtf(bc2);
+  const float inv_ws = 1.f / (float)ws;
+  const long long per = (nvec32 + ws - 1) / ws;
+  const long long lo = per * rank, hi = (lo + per < nvec32) ? lo + per : nvec32;
+  const long long stride = (long long)gridDim.x * kZThreads;
+  for (long long i0 = lo + (long long)blockIdx.x * kZThreads + threadIdx.x; i0 < hi; i0 += U * stride) {
+    v8 g[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < hi) {
+        if constexpr (WS == 0) {
+          mm_ld_reduce8(MC.grad + byte_off + i * 32, g[u]);
+        } else {
+          v8 part[WS];
+#pragma unroll
+          for (int r = 0; r < WS; ++r)
+            if (r < ws) part[r] = ldsys8(P.grad[r] + byte_off + i * 32);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            float a = 0.f;
+#pragma unroll
+            for (int r = 0; r < WS; ++r)
+              if (r < ws) a += part[r].f[k];
+            g[u].f[k] = a;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * stride;
+      if (i >= hi) continue;
+      const long long li = (i - lo) * 8;  // index into this rank's m / v slices
+      v8 pv = *reinterpret_cast<const v8*>(P.param[rank] + byte_off + i * 32);
+      v8 mv = *reinterpret_cast<const v8*>(m_slice + li);
+      v8 vv = *reinterpret_cast<const v8*>(v_slice + li);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float gk = g[u].f[k] * inv_ws;
+        const float mk = b1 * mv.f[k] + (1.f - b1) * gk;
+        const float vk = b2 * vv.f[k] + (1.f - b2) * gk * gk;
+        float pk = pv.f[k];
+        if (mode == 0) {
+          pk -= alpha_t * mk / (sqrtf(vk) + eps);
+          pk -= lr * wd * pk;
+        } else {
+          pk *= (1.f - lr * wd);
+          pk -= (lr / bc1) * mk / (sqrtf(vk) * rsqrt_bc2 + eps);
+        }
+        mv.f[k] = mk; vv.f[k] = vk; pv.f[k] = pk;
+      }
+      *reinterpret_cast<v8*>(m_slice + li) = mv;
+      *reinterpret_cast<v8*>(v_slice + li) = vv;
+      const uint32_t s0 = pack_bf16x2(pv.f[0], pv.f[1]), s1 = pack_bf16x2(pv.f[2], pv.f[3]);
+      const uint32_t s2 = pack_bf16x2(pv.f[4], pv.f[5]), s3 = pack_bf16x2(pv.f[6], pv.f[7]);
+      if constexpr (WS == 0) {
+        char* pa = MC.param + byte_off + i * 32;
+        mm_st4(pa, pv.f[0], pv.f[1], pv.f[2], pv.f[3]);
+        mm_st4(pa + 16, pv.f[4], pv.f[5], pv.f[6], pv.f[7]);
+        if (MC.shadow)
+          mm_st4(MC.shadow + (byte_off >> 1) + i * 16, __uint_as_float(s0), __uint_as_float(s1), __uint_as_float(s2),
+                 __uint_as_float(s3));
+      } else {
+#pragma unroll
+        for (int r = 0; r < WS; ++r)
+          if (r < ws) {
+            stsys8(P.param[r] + byte_off + i * 32, pv);
+            if (P.shadow[r]) stsys4u(P.shadow[r] + (byte_off >> 1) + i * 16, s0, s1, s2, s3);
+          }
+      }
+    }
+  }
+  zbarrier(P, rank, ws, slot);  // every owner's parameter stores have landed on every rank
+}
+
+__global__ void zero_incr_step_kernel(int* step) { *step += 1; }
+
+}  // namespace comm
+}  // namespace b200
+
 using namespace b200;
+
+extern "C" int b200_zero_adamw_bucket(const unsigned long long* grad_peers_host, const unsigned long long* param_peers_host,
+                                      const unsigned long long* shadow_peers_host /*nullable*/,
+                                      const unsigned long long* signal_ptrs_host, const unsigned long long* multicast3_host,
+                                      long long byte_off, long long numel, float* m_slice, float* v_slice,
+                                      const float* hyper_dev, const int* step_dev, int mode, int rank, int world_size,
+                                      int blocks, int signal_slot, void* stream) {
+  using namespace b200::comm;
+  B200_REQUIRE(world_size >= 1 && world_size <= kMaxRanksD, "zero_adamw: world size %d unsupported", world_size);
+  B200_REQUIRE(byte_off % 32 == 0, "zero_adamw: bucket offset must be 32-byte aligned");
+  if (numel <= 0) return 0;
+  ZPeers P;
+  for (int r = 0; r < kMaxRanksD; ++r) {
+    const bool on = r < world_size;
+    P.grad[r] = on ? reinterpret_cast<char*>(grad_peers_host[r]) : nullptr;
+    P.param[r] = on ? reinterpret_cast<char*>(param_peers_host[r]) : nullptr;
+    P.shadow[r] = (on && shadow_peers_host) ? reinterpret_cast<char*>(shadow_peers_host[r]) : nullptr;
+    P.sig[r] = on ? reinterpret_cast<unsigned int*>(signal_ptrs_host[r]) : nullptr;
+  }
+  ZMulticast MC{nullptr, nullptr, nullptr};
+  // NVLS needs the multicast mapping of the gradient and parameter arenas (and of the shadow arena when shadows
+  // are kept); with fewer the kernel uses plain peer loads/stores
+  const bool nvls = multicast3_host && multicast3_host[0] && multicast3_host[1] && (!shadow_peers_host || multicast3_host[2]);
+  if (nvls) {
+    MC.grad = reinterpret_cast<char*>(multicast3_host[0]);
+    MC.param = reinterpret_cast<char*>(multicast3_host[1]);
+    MC.shadow = shadow_peers_host ? reinterpret_cast<char*>(multicast3_host[2]) : nullptr;
+  }
+  const long long nvec32 = (numel * 4 + 31) / 32;
+  if (blocks <= 0) blocks = kZMaxBlocks;
+  if (blocks > kZMaxBlocks) blocks = kZMaxBlocks;
+  const long long want = (nvec32 / world_size + 2 * kZThreads - 1) / (2 * kZThreads);
+  if (want < blocks) blocks = (int)(want < 1 ? 1 : want);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+#define ZLAUNCH(WSV) zero_adamw_kernel<WSV><<<blocks, kZThreads, 0, s>>>(P, MC, byte_off, nvec32, m_slice, v_slice, hyper_dev, step_dev, mode, rank, world_size, signal_slot)
+  if (nvls) ZLAUNCH(0);
+  else if (world_size <= 2) ZLAUNCH(2);
+  else if (world_size <= 4) ZLAUNCH(4);
+  else ZLAUNCH(8);
+#undef ZLAUNCH
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200_incr_step(int* step_dev, void* stream) {
+  comm::zero_incr_step_kernel<<<1, 1, 0, reinterpret_cast<cudaStream_t>(stream)>>>(step_dev);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
 
 extern "C" int b200_adamw_multi_distribute(const b200_adamw_tensor* table_dev, const long long* chunk_start_dev,
                                            int n_tensors, long long total_chunks, const float* hyper_dev,

@@ -166,6 +166,20 @@ int b200_adamw_multi_distribute(const b200_adamw_tensor* table_dev, const long l
                                 unsigned long long local_param_base, unsigned long long local_shadow_base,
                                 int world_size, void* stream);
 
+/* One DDP bucket, one kernel: rank r averages slice r of the gradient bucket out of every rank's symmetric grad
+ * arena, applies AdamW with its slice of m / v (optimizer state sharded 1/world_size), and stores the new fp32
+ * parameters and bf16 shadows into every rank's parameter / shadow arenas (same element layout as the gradient
+ * bucket; shadow offset = byte_off / 2).  m_slice / v_slice: ceil(ceil(numel/8)/ws)*8 floats, this rank only.
+ * ref: all_reduce + grad/ws (…sharded.py:299,314) + optimizer.step + per-parameter broadcast (…:335-340). */
+int b200_zero_adamw_bucket(const unsigned long long* grad_peers_host, const unsigned long long* param_peers_host,
+                           const unsigned long long* shadow_peers_host /*nullable*/,
+                           const unsigned long long* signal_ptrs_host,
+                           const unsigned long long* multicast3_host /*nullable: NVLS addresses of grad, param, shadow arenas*/,
+                           long long byte_off, long long numel, float* m_slice, float* v_slice, const float* hyper_dev,
+                           const int* step_dev, int mode, int rank, int world_size, int blocks, int signal_slot,
+                           void* stream);
+int b200_incr_step(int* step_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
