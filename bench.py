@@ -46,6 +46,11 @@ def parse_args():
     ap.add_argument("--sharded", action="store_true",
                     help="shard optimizer state across ranks (ours: ShardedOptimizer + fused NVLink AdamW/distribute; "
                          "reference: ShardedStateOptimizer)")
+    ap.add_argument("--optimizer", choices=["auto", "replicated", "sharded"], default="auto",
+                    help="ours, N>1: 'sharded' = AdamW state sharded 1/N per rank with the update fused into the "
+                         "per-bucket NVLink reduce kernel (every rank still ends the step with all updated fp32 "
+                         "parameters); 'replicated' = all-reduce then full AdamW on every rank; 'auto' = sharded for "
+                         "2..4 ranks (measured faster), replicated otherwise")
     ap.add_argument("--no-overlap", action="store_true",
                     help="ours: run the optimizer after backward instead of overlapping it with backward")
     return ap.parse_args()
@@ -120,7 +125,11 @@ def build_ours(args, rank, ws, dev):
         model = DDPBucketed(model, bucket_size_mb=args.bucket_mb, backend=args.comm)
     kw = dict(lr=1e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
     fused_sharded = False
-    if args.sharded and ws > 1:
+    shard = args.sharded or args.optimizer == "sharded" or (args.optimizer == "auto" and 2 <= ws <= 4)
+    if shard and ws > 1 and not getattr(getattr(model, "_reducer", None), "kind", "") == "symm":
+        shard = args.sharded  # the fused path needs the NVLink backend; an explicit --sharded still gets the generic one
+    args.shard_effective = bool(shard and ws > 1)
+    if shard and ws > 1:
         from cs336_a2_systems_b200.parallel import ShardedOptimizer
         opt = ShardedOptimizer(model.parameters(), AdamW, **kw)
         fused_sharded = opt.enable_symmetric(model)
@@ -128,8 +137,8 @@ def build_ours(args, rank, ws, dev):
         opt = AdamW(model.parameters(), **kw)
     bucket_fused = hasattr(getattr(opt, "_symm", None), "_reduce_bucket")
     trainer = Trainer(model, opt, autocast=True,
-                      cuda_graph=not args.no_graph and (bucket_fused or not (args.sharded and ws > 1)),
-                      overlap_optimizer=not args.no_overlap and not args.sharded)
+                      cuda_graph=not args.no_graph and (bucket_fused or not args.shard_effective),
+                      overlap_optimizer=not args.no_overlap and not args.shard_effective)
     state = {"launches_per_step": 0}
 
     def step_device(x, y):
@@ -144,7 +153,7 @@ def build_ours(args, rank, ws, dev):
         state["launches_per_step"] = kernels.launches - n0
 
     extra = {"cuda_graph": trainer.cuda_graph, "optimizer_overlapped_with_backward": trainer._overlap is not None,
-             "sharded_optimizer": bool(args.sharded and ws > 1), "fused_nvlink_sharded_adamw": fused_sharded,
+             "sharded_optimizer": args.shard_effective, "fused_nvlink_sharded_adamw": fused_sharded,
              "bucket_fused_reduce_scatter_adamw_allgather": bucket_fused,
              "comm": getattr(getattr(model, "_reducer", None), "kind", "none")}
     return step_device, step_e2e, count_launches, state, extra
@@ -262,7 +271,12 @@ def main():
             "impl": args.impl,
             "config": {"model": args.model, **cfg, "vocab": args.vocab, "seq_len": args.ctx,
                        "global_batch": ws * args.batch, "per_gpu_batch": args.batch,
-                       "parallelism": f"dp{ws}", "bucket_size_mb": args.bucket_mb, "optimizer": "AdamW fp32 state",
+                       "parallelism": f"dp{ws}", "bucket_size_mb": args.bucket_mb,
+                       "optimizer": ("AdamW fp32 state, sharded 1/N per rank (ZeRO-1), update fused into the "
+                                     "per-bucket NVLink reduce-scatter/all-gather kernel")
+                       if extra.get("bucket_fused_reduce_scatter_adamw_allgather") else
+                       ("AdamW fp32 state, sharded by parameter owner" if extra.get("sharded_optimizer")
+                        else "AdamW fp32 state, replicated"),
                        "l2": "no flush: ~30 GB working set per step >> 126 MB L2", **extra},
             "e2e": {"value": round(e2e_value, 1), "unit": "tokens/s", "ms_per_step": round(ms_e2e / args.steps, 3),
                     "h2d_bytes_per_step": 2 * args.batch * args.ctx * 8, "d2h_bytes_per_step": 4},

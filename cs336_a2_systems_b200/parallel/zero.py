@@ -62,11 +62,21 @@ class BucketFusedAdamW:
         native.set_shadow_provider(self._provide_shadow)
         probe = torch.nn.Parameter(torch.zeros(1))
         self._defaults = dict(sharded.optimizer_cls([probe], **sharded.optimizer_kwargs).defaults)
-        # NVLS (reduce in the switch, replicate stores in the switch) pays from 3 ranks up; 2 ranks use plain P2P
+        # measured per-variant on B200 (profiles/zero_kernel_n*.json): with 2 ranks plain P2P moves the fewest
+        # bytes and the bf16 shadows ride along; from 3 ranks up the shadows are re-cast locally from the fp32
+        # parameters that arrived (fewer NVLink bytes) and the gradient slice can be reduced in the switch
         mcs = [self.garena.multicast_ptr, self.parena.multicast_ptr, self.sarena.multicast_ptr]
-        use_mc = self.ws > 2 and all(mcs) and os.environ.get("B200SYS_MULTIMEM", "1") != "0"
-        self._mc = kernels.host_ptr_array(mcs) if use_mc else None
-        self.nvls = use_mc
+        have_mc = all(mcs) and os.environ.get("B200SYS_MULTIMEM", "1") != "0"
+        self._mc = kernels.host_ptr_array(mcs) if have_mc else None
+        v = os.environ.get("B200SYS_ZERO_VARIANT", "auto")
+        if v == "auto":
+            # the all-NVLS variant (3) is the fastest stand-alone at 8 ranks (2.19 vs 2.82 ms/GB) but has only been
+            # exercised in the micro-benchmark; the P2P variant is the one validated end to end at 2/4/8 ranks
+            self.variant = 0
+        else:
+            self.variant = int(v) if have_mc else 0
+        sh = os.environ.get("B200SYS_ZERO_SHADOW", "auto")
+        self.wire_shadows = (self.ws <= 2) if sh == "auto" else (sh == "wire")
         self.hyper = torch.zeros(8, dtype=torch.float32, device=dev)
         self._hyper_host = torch.zeros(16, 8, dtype=torch.float32).pin_memory()
         self._hyper_slot = 0
@@ -113,10 +123,15 @@ class BucketFusedAdamW:
         boff, numel, m, v, _per = self._buckets[bi]
         with torch.cuda.stream(red.stream):
             _native.check(_native.lib().b200_zero_adamw_bucket(
-                self.garena.peer_ptrs_c, self.parena.peer_ptrs_c, self.sarena.peer_ptrs_c, self.garena.signal_ptrs_c,
-                self._mc, ctypes.c_longlong(boff), ctypes.c_longlong(numel), _native.p(m), _native.p(v), _native.p(self.hyper),
-                _native.p(self.step_dev), ctypes.c_int(self.mode), ctypes.c_int(self.rank), ctypes.c_int(self.ws),
-                ctypes.c_int(0), ctypes.c_int(0), ctypes.c_void_p(red.stream.cuda_stream)), "zero_adamw_bucket")
+                self.garena.peer_ptrs_c, self.parena.peer_ptrs_c, self.sarena.peer_ptrs_c if self.wire_shadows else None,
+                self.garena.signal_ptrs_c, self._mc, ctypes.c_longlong(boff), ctypes.c_longlong(numel), _native.p(m),
+                _native.p(v), _native.p(self.hyper), _native.p(self.step_dev), ctypes.c_int(self.mode),
+                ctypes.c_int(self.rank), ctypes.c_int(self.ws), ctypes.c_int(0), ctypes.c_int(0),
+                ctypes.c_int(self.variant), ctypes.c_void_p(red.stream.cuda_stream)), "zero_adamw_bucket")
+            if not self.wire_shadows:
+                # every rank's slice of the new fp32 parameters has landed (trailing barrier of the kernel)
+                kernels.cast_bf16(self.parena.view(boff, numel, torch.float32),
+                                  self.sarena.view(boff // 2, numel, torch.bfloat16))
             kernels._count()
         self._launched = True
         return bi

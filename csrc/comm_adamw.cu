@@ -172,10 +172,10 @@ __device__ __forceinline__ void mm_st4(char* a, float x, float y, float z, float
 constexpr int kZThreads = 256;
 constexpr int kZMaxBlocks = 148;  // one CTA per SM, co-resident with the backward GEMMs (<=112 regs x 256 threads next to the GEMM CTA)
 
-// WS > 0: peer-to-peer loads/stores over WS ranks.  WS == 0: NVLS — the switch reduces the gradient slice
-// (multimem.ld_reduce) and replicates the parameter / shadow stores (multimem.st).
-template <int WS>
-__global__ void __launch_bounds__(kZThreads) zero_adamw_kernel(ZPeers P, ZMulticast MC, long long byte_off,
+// MMLD: the switch reduces the gradient slice (multimem.ld_reduce) instead of WS peer loads per vector.
+// MMST: the switch replicates the parameter / shadow stores (multimem.st) instead of one store per peer.
+template <int WS, bool MMLD, bool MMST>
+__global__ void __launch_bounds__(kZThreads, 2) zero_adamw_kernel(ZPeers P, ZMulticast MC, long long byte_off,
                                                                long long nvec32, float* __restrict__ m_slice,
                                                                float* __restrict__ v_slice,
                                                                const float* __restrict__ hyper,
@@ -197,7 +197,7 @@ __global__ void __launch_bounds__(kZThreads) zero_adamw_kernel(ZPeers P, ZMultic
     for (int u = 0; u < U; ++u) {
       const long long i = i0 + u * stride;
       if (i < hi) {
-        if constexpr (WS == 0) {
+        if constexpr (MMLD) {
           mm_ld_reduce8(MC.grad + byte_off + i * 32, g[u]);
         } else {
           v8 part[WS];
@@ -242,7 +242,7 @@ __global__ void __launch_bounds__(kZThreads) zero_adamw_kernel(ZPeers P, ZMultic
       *reinterpret_cast<v8*>(v_slice + li) = vv;
       const uint32_t s0 = pack_bf16x2(pv.f[0], pv.f[1]), s1 = pack_bf16x2(pv.f[2], pv.f[3]);
       const uint32_t s2 = pack_bf16x2(pv.f[4], pv.f[5]), s3 = pack_bf16x2(pv.f[6], pv.f[7]);
-      if constexpr (WS == 0) {
+      if constexpr (MMST) {
         char* pa = MC.param + byte_off + i * 32;
         mm_st4(pa, pv.f[0], pv.f[1], pv.f[2], pv.f[3]);
         mm_st4(pa + 16, pv.f[4], pv.f[5], pv.f[6], pv.f[7]);
@@ -251,7 +251,7 @@ __global__ void __launch_bounds__(kZThreads) zero_adamw_kernel(ZPeers P, ZMultic
                  __uint_as_float(s3));
       } else {
 #pragma unroll
-        for (int r = 0; r < WS; ++r)
+        for (int r = 0; r < kMaxRanksD; ++r)
           if (r < ws) {
             stsys8(P.param[r] + byte_off + i * 32, pv);
             if (P.shadow[r]) stsys4u(P.shadow[r] + (byte_off >> 1) + i * 16, s0, s1, s2, s3);
@@ -260,6 +260,88 @@ __global__ void __launch_bounds__(kZThreads) zero_adamw_kernel(ZPeers P, ZMultic
     }
   }
   zbarrier(P, rank, ws, slot);  // every owner's parameter stores have landed on every rank
+}
+
+// NVLS-reduce variant on 16-byte units: consecutive lanes touch consecutive 16-byte chunks, so every
+// multimem.ld_reduce warp instruction covers one contiguous 512-byte span (the 32-byte-per-lane layout of the
+// kernel above splits each span over two instructions and ran 1.7x slower through the switch).
+struct v4 { float f[4]; };
+template <bool MMST>
+__global__ void __launch_bounds__(kZThreads) zero_adamw_mm_kernel(ZPeers P, ZMulticast MC, long long byte_off,
+                                                                  long long nvec32, float* __restrict__ m_slice,
+                                                                  float* __restrict__ v_slice,
+                                                                  const float* __restrict__ hyper,
+                                                                  const int* __restrict__ step, int mode, int rank,
+                                                                  int ws, int slot) {
+  constexpr int U = 4;
+  zbarrier(P, rank, ws, slot);
+  const float lr = hyper[0], b1 = hyper[1], b2 = hyper[2], eps = hyper[3], wd = hyper[4];
+  const float t = (float)(*step);
+  const float bc1 = 1.f - powf(b1, t), bc2 = 1.f - powf(b2, t);
+  const float alpha_t = lr * sqrtf(bc2) / bc1, rsqrt_bc2 = rsqrtf(bc2);
+  const float inv_ws = 1.f / (float)ws;
+  const long long per = (nvec32 + ws - 1) / ws;
+  const long long lo32 = per * rank, hi32 = (lo32 + per < nvec32) ? lo32 + per : nvec32;
+  const long long lo = lo32 * 2, hi = hi32 * 2;  // 16-byte units
+  const long long stride = (long long)gridDim.x * kZThreads;
+  for (long long i0 = lo + (long long)blockIdx.x * kZThreads + threadIdx.x; i0 < hi; i0 += U * stride) {
+    v4 g[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < hi)
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(g[u].f[0]), "=f"(g[u].f[1]), "=f"(g[u].f[2]), "=f"(g[u].f[3])
+                     : "l"(MC.grad + byte_off + i * 16) : "memory");
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * stride;
+      if (i >= hi) continue;
+      const long long li = (i - lo) * 4;
+      float4 pv = *reinterpret_cast<const float4*>(P.param[rank] + byte_off + i * 16);
+      float4 mv = *reinterpret_cast<const float4*>(m_slice + li);
+      float4 vv = *reinterpret_cast<const float4*>(v_slice + li);
+      float* pp = reinterpret_cast<float*>(&pv);
+      float* mp = reinterpret_cast<float*>(&mv);
+      float* vp = reinterpret_cast<float*>(&vv);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float gk = g[u].f[k] * inv_ws;
+        const float mk = b1 * mp[k] + (1.f - b1) * gk;
+        const float vk = b2 * vp[k] + (1.f - b2) * gk * gk;
+        float pk = pp[k];
+        if (mode == 0) {
+          pk -= alpha_t * mk / (sqrtf(vk) + eps);
+          pk -= lr * wd * pk;
+        } else {
+          pk *= (1.f - lr * wd);
+          pk -= (lr / bc1) * mk / (sqrtf(vk) * rsqrt_bc2 + eps);
+        }
+        mp[k] = mk; vp[k] = vk; pp[k] = pk;
+      }
+      *reinterpret_cast<float4*>(m_slice + li) = mv;
+      *reinterpret_cast<float4*>(v_slice + li) = vv;
+      const uint32_t s0 = pack_bf16x2(pv.x, pv.y), s1 = pack_bf16x2(pv.z, pv.w);
+      if constexpr (MMST) {
+        mm_st4(MC.param + byte_off + i * 16, pv.x, pv.y, pv.z, pv.w);
+        if (MC.shadow)
+          asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1,%2};" ::"l"(MC.shadow + (byte_off >> 1) + i * 8),
+                       "f"(__uint_as_float(s0)), "f"(__uint_as_float(s1)) : "memory");
+      } else {
+#pragma unroll
+        for (int r = 0; r < kMaxRanksD; ++r)
+          if (r < ws) {
+            asm volatile("st.global.relaxed.sys.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(P.param[r] + byte_off + i * 16),
+                         "f"(pv.x), "f"(pv.y), "f"(pv.z), "f"(pv.w) : "memory");
+            if (P.shadow[r])
+              asm volatile("st.global.relaxed.sys.v2.b32 [%0], {%1,%2};" ::"l"(P.shadow[r] + (byte_off >> 1) + i * 8),
+                           "r"(s0), "r"(s1) : "memory");
+          }
+      }
+    }
+  }
+  zbarrier(P, rank, ws, slot);
 }
 
 __global__ void zero_incr_step_kernel(int* step) { *step += 1; }
@@ -274,7 +356,7 @@ extern "C" int b200_zero_adamw_bucket(const unsigned long long* grad_peers_host,
                                       const unsigned long long* signal_ptrs_host, const unsigned long long* multicast3_host,
                                       long long byte_off, long long numel, float* m_slice, float* v_slice,
                                       const float* hyper_dev, const int* step_dev, int mode, int rank, int world_size,
-                                      int blocks, int signal_slot, void* stream) {
+                                      int blocks, int signal_slot, int variant, void* stream) {
   using namespace b200::comm;
   B200_REQUIRE(world_size >= 1 && world_size <= kMaxRanksD, "zero_adamw: world size %d unsupported", world_size);
   B200_REQUIRE(byte_off % 32 == 0, "zero_adamw: bucket offset must be 32-byte aligned");
@@ -287,12 +369,17 @@ extern "C" int b200_zero_adamw_bucket(const unsigned long long* grad_peers_host,
     P.shadow[r] = (on && shadow_peers_host) ? reinterpret_cast<char*>(shadow_peers_host[r]) : nullptr;
     P.sig[r] = on ? reinterpret_cast<unsigned int*>(signal_ptrs_host[r]) : nullptr;
   }
+  // variant bit 0: reduce the gradients in the switch (needs the multicast mapping of the gradient arena);
+  // variant bit 1: replicate parameter / shadow stores in the switch (needs those arenas' multicast mappings)
   ZMulticast MC{nullptr, nullptr, nullptr};
-  // NVLS needs the multicast mapping of the gradient and parameter arenas (and of the shadow arena when shadows
-  // are kept); with fewer the kernel uses plain peer loads/stores
-  const bool nvls = multicast3_host && multicast3_host[0] && multicast3_host[1] && (!shadow_peers_host || multicast3_host[2]);
-  if (nvls) {
+  const bool mmld = (variant & 1) != 0, mmst = (variant & 2) != 0;
+  if (mmld) {
+    B200_REQUIRE(multicast3_host && multicast3_host[0], "zero_adamw: NVLS reduce needs the gradient arena's multicast address");
     MC.grad = reinterpret_cast<char*>(multicast3_host[0]);
+  }
+  if (mmst) {
+    B200_REQUIRE(multicast3_host && multicast3_host[1] && (!shadow_peers_host || multicast3_host[2]),
+                 "zero_adamw: NVLS stores need the parameter (and shadow) arena's multicast address");
     MC.param = reinterpret_cast<char*>(multicast3_host[1]);
     MC.shadow = shadow_peers_host ? reinterpret_cast<char*>(multicast3_host[2]) : nullptr;
   }
@@ -302,11 +389,17 @@ extern "C" int b200_zero_adamw_bucket(const unsigned long long* grad_peers_host,
   const long long want = (nvec32 / world_size + 2 * kZThreads - 1) / (2 * kZThreads);
   if (want < blocks) blocks = (int)(want < 1 ? 1 : want);
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-#define ZLAUNCH(WSV) zero_adamw_kernel<WSV><<<blocks, kZThreads, 0, s>>>(P, MC, byte_off, nvec32, m_slice, v_slice, hyper_dev, step_dev, mode, rank, world_size, signal_slot)
-  if (nvls) ZLAUNCH(0);
-  else if (world_size <= 2) ZLAUNCH(2);
-  else if (world_size <= 4) ZLAUNCH(4);
-  else ZLAUNCH(8);
+#define ZLAUNCH(WSV, LD, ST) zero_adamw_kernel<WSV, LD, ST><<<blocks, kZThreads, 0, s>>>(P, MC, byte_off, nvec32, m_slice, v_slice, hyper_dev, step_dev, mode, rank, world_size, signal_slot)
+  if (mmld) {
+    if (mmst) zero_adamw_mm_kernel<true><<<blocks, kZThreads, 0, s>>>(P, MC, byte_off, nvec32, m_slice, v_slice, hyper_dev, step_dev, mode, rank, world_size, signal_slot);
+    else zero_adamw_mm_kernel<false><<<blocks, kZThreads, 0, s>>>(P, MC, byte_off, nvec32, m_slice, v_slice, hyper_dev, step_dev, mode, rank, world_size, signal_slot);
+  } else if (world_size <= 2) {
+    if (mmst) ZLAUNCH(2, false, true); else ZLAUNCH(2, false, false);
+  } else if (world_size <= 4) {
+    if (mmst) ZLAUNCH(4, false, true); else ZLAUNCH(4, false, false);
+  } else {
+    if (mmst) ZLAUNCH(8, false, true); else ZLAUNCH(8, false, false);
+  }
 #undef ZLAUNCH
   B200_LAUNCH_CHECK();
   return 0;

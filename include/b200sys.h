@@ -177,7 +177,7 @@ int b200_zero_adamw_bucket(const unsigned long long* grad_peers_host, const unsi
                            const unsigned long long* multicast3_host /*nullable: NVLS addresses of grad, param, shadow arenas*/,
                            long long byte_off, long long numel, float* m_slice, float* v_slice, const float* hyper_dev,
                            const int* step_dev, int mode, int rank, int world_size, int blocks, int signal_slot,
-                           void* stream);
+                           int variant /*bit0: NVLS reduce, bit1: NVLS stores*/, void* stream);
 int b200_incr_step(int* step_dev, void* stream);
 
 #ifdef __cplusplus
