@@ -119,3 +119,20 @@ def test_checkpoint_roundtrip_and_generate(tmp_path):
 def test_presets():
     assert get_model_config("xl") == dict(d_model=1600, d_ff=6400, num_layers=48, num_heads=25)
     assert get_model_config("2.7B")["d_model"] == 2560
+
+
+def test_lm_forward_backward_snapshot(array_snapshot):
+    """Pins the CPU numerics of the LM (logits, loss, two gradients) against a stored array snapshot, so a
+    refactor of layers / init / RoPE layout that changes results is caught even when it stays self-consistent."""
+    torch.manual_seed(1234)
+    m = TransformerLM(vocab_size=64, context_length=16, d_model=32, num_layers=2, num_heads=4, d_ff=64)
+    g = torch.Generator().manual_seed(5)
+    x = torch.randint(0, 64, (2, 16), generator=g)
+    y = torch.roll(x, -1, 1)
+    logits = m(x)
+    loss = cross_entropy(logits, y)
+    loss.backward()
+    array_snapshot.assert_match({
+        "logits": logits, "loss": loss,
+        "grad_q0": m.layers[0].attn.q_proj.weight.grad, "grad_ln_final": m.ln_final.weight.grad,
+    }, rtol=1e-4, atol=1e-5)

@@ -1,3 +1,6 @@
+"""Two-rank debugging aid: trains the same tiny LM with (a) NVLink DDP + replicated AdamW and (b) the bucket-fused
+ZeRO-1 step, and prints the per-parameter max difference after every step.  Run on a 2-GPU box:
+``python tools/zero_debug.py``."""
 import copy, os, sys
 import torch, torch.distributed as dist, torch.multiprocessing as mp
 sys.path.insert(0, os.getcwd())
