@@ -6,11 +6,11 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from cs336_a2_systems_b200.ops import kernels as k, functional as F_ref
 
-which = set(sys.argv[1:]) or {"gemm", "fa", "norm", "swiglu", "adamw"}
+which = set(sys.argv[1:]) or {"gemm", "pair", "fa", "norm", "swiglu", "adamw"}
 dev = "cuda"
 T, d, dff, H, dh, B, S = 2048, 1600, 6400, 25, 64, 4, 512
 bf = lambda *s: torch.randn(*s, device=dev).bfloat16()
-reps = 2
+reps = int(os.environ.get("NCU_REPS", "2"))
 if "gemm" in which:
     x, w = bf(T, d), bf(3 * d, d) * 0.05
     for _ in range(reps):
@@ -24,6 +24,19 @@ if "gemm" in which:
     dy2, out2 = bf(T, dff), torch.empty(dff, d, device=dev)
     for _ in range(reps):
         k.gemm(dy2, x1, a_mn=True, b_mn=True, epilogue=k.EPI_F32, out=out2)  # wgrad TN 6400x1600x2048
+if "pair" in which:
+    # CTA-pair (cta_group::2) kernel, forced: fwd NT 2048x12800x1600 (w1|w3) and dgrad NN 2048x1600x12800
+    x, w13 = bf(T, d), bf(2 * dff, d) * 0.05
+    for _ in range(reps):
+        k.gemm(x, w13, pair=True)
+    dy = bf(T, 2 * dff)
+    for _ in range(reps):
+        k.gemm(dy, w13, b_mn=True, pair=True)
+if "xent" in which:
+    logits, tgt = bf(T, 10000), torch.randint(0, 10000, (T,), device=dev)
+    for _ in range(reps):
+        loss, lse = k.xent_fwd(logits, tgt)
+        k.xent_bwd(logits, tgt, lse, torch.ones((), device=dev))
 if "fa" in which:
     qkv = bf(B, S, 3, H, dh)
     q, kk, v = (qkv[:, :, i].permute(0, 2, 1, 3) for i in range(3))
