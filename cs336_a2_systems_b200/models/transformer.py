@@ -41,8 +41,8 @@ def get_model_config(size: str) -> dict[str, int]:
 def build_lm(size: str = "small", vocab_size: int = 10000, context_length: int = 512,
              rope_theta: float = 10000.0, device=None) -> "TransformerLM":
     cfg = get_model_config(size)
-    if device is not None and torch.device(device).type == "cuda":
-        # initialise on the GPU: trunc_normal_ of 2B parameters on the host is minutes
+    if device is not None and torch.device(device).type in ("cuda", "meta"):
+        # initialise on the GPU: trunc_normal_ of 2B parameters on the host is minutes ("meta": shapes only)
         with torch.device(device):
             return TransformerLM(vocab_size=vocab_size, context_length=context_length,
                                  rope_theta=rope_theta, **cfg)

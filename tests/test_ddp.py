@@ -29,3 +29,21 @@ def test_bucket_planner():
     assert plan_buckets(ps, 1 * mb) == [[0], [1], [2], [3], [4]]     # tiny cap: one per tensor
     mixed = [torch.zeros(4), torch.zeros(4, dtype=torch.float64), torch.zeros(4)]
     assert plan_buckets(mixed, None) == [[0], [1], [2]]              # dtype change closes a bucket
+
+
+@pytest.mark.parametrize("size,expected", [("small", [98, 50, 6, 1]), ("xl", [386, 339, 98, 8]),
+                                           ("2.7b", [258, 258, 161, 14])])
+def test_bucket_counts_match_reference_algorithm(size, expected):
+    """The greedy reverse-order bucketing of the reference (``ddp_bucketed_overlapped_sharded.py:265-279``) yields
+    these bucket counts for bucket_size_mb = 1/10/100/1000; ours must plan the same buckets."""
+    import torch
+    from cs336_a2_systems_b200.models import build_lm
+    from cs336_a2_systems_b200.parallel.ddp import plan_buckets
+
+    m = build_lm(size, vocab_size=10000, context_length=512, device="meta")
+    order = list(reversed([p for p in m.parameters() if p.requires_grad]))
+    assert [len(plan_buckets(order, mb)) for mb in (1, 10, 100, 1000)] == expected
+    # every parameter lands in exactly one bucket
+    for mb in (1, 100):
+        idx = sorted(i for b in plan_buckets(order, mb) for i in b)
+        assert idx == list(range(len(order)))
