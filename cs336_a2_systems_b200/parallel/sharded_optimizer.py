@@ -178,6 +178,9 @@ class ShardedOptimizer(torch.optim.Optimizer):
 
     def load_consolidated_state_dict(self, sd: dict) -> None:
         """Inverse of :meth:`consolidated_state_dict`: every rank keeps only what it owns."""
+        if hasattr(self._symm, "load_full_state"):
+            self._symm.load_full_state(sd["state"])
+            return
         if self.optimizer is None:
             return
         index = {}

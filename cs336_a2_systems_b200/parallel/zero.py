@@ -28,6 +28,34 @@ from ..ops import kernels, native
 from . import symm
 
 
+def slice_floats(numel: int, world_size: int) -> int:
+    """fp32 elements of one rank's slice of a bucket of ``numel`` elements: the kernel splits the bucket into
+    32-byte vectors and gives each rank ``ceil(nvec / world_size)`` consecutive ones."""
+    nvec = (numel * 4 + 31) // 32
+    return (nvec + world_size - 1) // world_size * 8
+
+
+def split_bucket_state(full: torch.Tensor, shapes, offsets):
+    """Per-parameter views of a bucket-layout flat tensor (``offsets`` in elements, as in ``DDPBucketed``)."""
+    out = []
+    for shape, off in zip(shapes, offsets):
+        n = 1
+        for d in shape:
+            n *= d
+        out.append(full[off:off + n].view(shape))
+    return out
+
+
+def assemble_bucket_state(tensors, offsets, total: int, device=None) -> torch.Tensor:
+    """Inverse of :func:`split_bucket_state`: a zero-padded flat tensor of ``total`` elements holding
+    ``tensors[i]`` at ``offsets[i]`` (None entries stay zero)."""
+    full = torch.zeros(total, dtype=torch.float32, device=device)
+    for t, off in zip(tensors, offsets):
+        if t is not None:
+            full[off:off + t.numel()].copy_(t.reshape(-1))
+    return full
+
+
 class BucketFusedAdamW:
     def __init__(self, sharded, ddp, mode: int):
         red = ddp._reducer
@@ -52,11 +80,10 @@ class BucketFusedAdamW:
                     view.copy_(p.data)
                     p.data = view
                     self._off_of[id(p)] = byte
-                nvec = (b.numel * 4 + 31) // 32
-                per = (nvec + self.ws - 1) // self.ws
-                m = torch.zeros(per * 8, dtype=torch.float32, device=dev)
-                v = torch.zeros(per * 8, dtype=torch.float32, device=dev)
-                self._buckets.append((boff, b.numel, m, v, per))
+                per8 = slice_floats(b.numel, self.ws)
+                m = torch.zeros(per8, dtype=torch.float32, device=dev)
+                v = torch.zeros(per8, dtype=torch.float32, device=dev)
+                self._buckets.append((boff, b.numel, m, v, per8))
         self._params = [p for b in ddp.buckets for p in b.params]
         native.drop_shadows(self._params)
         native.set_shadow_provider(self._provide_shadow)
@@ -157,24 +184,49 @@ class BucketFusedAdamW:
                         ent.versions[i] = None
 
     # ------------------------------------------------------------------ state for checkpoints
-    def full_state(self):
-        """``{param_index: {"m", "v", "t"}}`` reassembled from the bucket slices (collective)."""
-        out = {}
+    def _param_index(self):
         index = {}
         i = 0
-        t = int(self.step_dev.item())  # device-resident: stays right under CUDA-graph replay
         for g in self.sharded.param_groups:
             for p in g["params"]:
                 index[id(p)] = i
                 i += 1
+        return index
+
+    def full_state(self):
+        """``{param_index: {"m", "v", "t"}}`` reassembled from the bucket slices (collective)."""
+        out = {}
+        index = self._param_index()
+        t = int(self.step_dev.item())  # device-resident: stays right under CUDA-graph replay
         for bi, b in enumerate(self.ddp.buckets):
-            _boff, numel, m, v, per = self._buckets[bi]
-            full_m = torch.empty(per * 8 * self.ws, device=self.device)
-            full_v = torch.empty(per * 8 * self.ws, device=self.device)
+            _boff, _numel, m, v, per8 = self._buckets[bi]
+            full_m = torch.empty(per8 * self.ws, device=self.device)
+            full_v = torch.empty(per8 * self.ws, device=self.device)
             dist.all_gather_into_tensor(full_m, m, group=self.garena.group)
             dist.all_gather_into_tensor(full_v, v, group=self.garena.group)
-            for p, off in zip(b.params, b.offsets):
+            shapes = [p.shape for p in b.params]
+            for p, pm, pv in zip(b.params, split_bucket_state(full_m, shapes, b.offsets),
+                                 split_bucket_state(full_v, shapes, b.offsets)):
                 if id(p) in index:
-                    out[index[id(p)]] = {"m": full_m[off:off + p.numel()].view(p.shape).cpu(),
-                                         "v": full_v[off:off + p.numel()].view(p.shape).cpu(), "t": t}
+                    out[index[id(p)]] = {"m": pm.cpu(), "v": pv.cpu(), "t": t}
         return out
+
+    @torch.no_grad()
+    def load_full_state(self, state: dict) -> None:
+        """Inverse of :meth:`full_state`: every rank keeps its slice of each bucket's m and v (no communication;
+        every rank reads the same consolidated dict)."""
+        index = self._param_index()
+        t = None
+        for bi, b in enumerate(self.ddp.buckets):
+            _boff, _numel, m, v, per8 = self._buckets[bi]
+            sts = [state.get(index.get(id(p), -1)) or state.get(str(index.get(id(p), -1))) for p in b.params]
+            for key, dst in (("m", m), ("v", v)):
+                full = assemble_bucket_state([None if st is None else st[key].to(torch.float32) for st in sts],
+                                             b.offsets, per8 * self.ws)
+                dst.copy_(full[self.rank * per8:(self.rank + 1) * per8])
+            for st in sts:
+                if st is not None and "t" in st:
+                    t = int(st["t"])
+        if t is not None:
+            self.step_dev.fill_(t)
+            self.t = t

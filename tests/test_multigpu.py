@@ -120,6 +120,16 @@ def _ddp_worker(rank, ws, port):
         ref_opt = opts["c10d"]
         p0 = next(models["c10d"].module.parameters())
         torch.testing.assert_close(full["state"][0]["m"].to(dev), ref_opt.state[p0]["m"], rtol=2e-3, atol=1e-5)
+    # checkpoint round trip of the slice-sharded state: consolidate on rank 0, hand everyone the dict, reload
+    box = [full]
+    dist.broadcast_object_list(box, src=0)
+    before = [(m.clone(), v.clone()) for _o, _n, m, v, _p in zo._symm._buckets]
+    for _o, _n, m, v, _p in zo._symm._buckets:
+        m.zero_()
+        v.zero_()
+    zo.load_consolidated_state_dict(box[0])
+    for (m0, v0), (_o, _n, m, v, _p) in zip(before, zo._symm._buckets):
+        assert torch.equal(m0, m) and torch.equal(v0, v)
     dist.barrier()
     dist.destroy_process_group()
 

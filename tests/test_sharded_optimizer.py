@@ -12,3 +12,27 @@ from .common import ToyModel, ToyModelWithTiedWeights
 def test_sharded_optimizer(model_cls):
     world_size = 2
     mp.spawn(sharded_worker, args=(world_size, find_free_port(), model_cls), nprocs=world_size, join=True)
+
+
+def test_zero_bucket_slice_arithmetic():
+    """Pure bookkeeping of the bucket-fused ZeRO path (parallel/zero.py): rank slices tile the bucket, and
+    per-parameter optimizer state survives assemble -> slice -> gather -> split."""
+    import torch
+    from cs336_a2_systems_b200.parallel.zero import assemble_bucket_state, slice_floats, split_bucket_state
+
+    g = torch.Generator().manual_seed(0)
+    shapes = [(5, 7), (3,), (16, 8), (1, 1)]
+    offsets, numel = [], 0
+    for sh in shapes:  # 32-byte aligned slots, like DDPBucketed
+        offsets.append(numel)
+        n = int(torch.tensor(sh).prod())
+        numel += (n + 7) // 8 * 8
+    for ws in (1, 2, 3, 4, 8):
+        per8 = slice_floats(numel, ws)
+        assert per8 % 8 == 0 and per8 * ws >= numel and per8 * (ws - 1) < numel + 8 * ws
+        state = [torch.randn(sh, generator=g) for sh in shapes]
+        full = assemble_bucket_state(state, offsets, per8 * ws)
+        slices = [full[r * per8:(r + 1) * per8].clone() for r in range(ws)]  # what each rank keeps
+        back = split_bucket_state(torch.cat(slices), shapes, offsets)       # what all_gather + split returns
+        for a, b in zip(state, back):
+            torch.testing.assert_close(a, b, rtol=0, atol=0)
