@@ -128,6 +128,9 @@ class SwiGLU(nn.Module):
         if native_active(x):
             from ..ops import native
 
+            if not torch.is_grad_enabled():  # serving / eval: the gate runs in the GEMM epilogue
+                h = native.swiglu_linear_nograd(x, self.w1.weight, self.w3.weight)
+                return native.linear(h, (self.w2.weight,))
             ab = native.linear(x, (self.w1.weight, self.w3.weight))  # one GEMM → [.., 2*d_ff]
             return native.linear(native.swiglu(ab), (self.w2.weight,))
         return self.w2(F_ref.silu(self.w1(x)) * self.w3(x))

@@ -29,6 +29,16 @@ GEMM_PAIR = _environ.get("B200SYS_GEMM_PAIR", "auto")  # "auto": per-shape choic
 launches = 0
 
 
+#: bumped whenever a fused optimizer kernel may have rewritten parameters behind autograd's back (raw-pointer
+#: launches do not touch ``Tensor._version``); caches derived from parameter values key on it
+param_epoch = 0
+
+
+def bump_param_epoch() -> None:
+    global param_epoch
+    param_epoch += 1
+
+
 def _count(n: int = 1) -> None:
     global launches
     launches += n
@@ -337,6 +347,7 @@ class AdamWLaunch:
                                            c_int(self.mode), c_int(1), c_int(max_blocks), stream_ptr()),
               "adamw_multi")
         _count(2)
+        bump_param_epoch()
 
 
 def clip_grad_norm(grads: list[Tensor], max_norm: float, eps: float, table: TensorTable | None = None) -> Tensor:
@@ -465,3 +476,4 @@ def adamw_multi_distribute(launch: "AdamWLaunch", param_arena, shadow_arena) -> 
         ctypes.c_ulonglong(shadow_arena.bytes.data_ptr() if shadow_arena is not None else 0),
         c_int(param_arena.world_size), stream_ptr()), "adamw_multi_distribute")
     _count(2)
+    bump_param_epoch()

@@ -313,6 +313,33 @@ def swiglu(ab: Tensor) -> Tensor:
     return SwiGLUFn.apply(ab)
 
 
+def gated_shadow(w1: Tensor, w3: Tensor) -> Tensor:
+    """bf16 ``[2*d_ff, d]`` with the rows of w1 and w3 interleaved (w1[0], w3[0], w1[1], ...): the B operand of the
+    GEMM whose epilogue applies ``silu(gate) * up`` (``EPI_BF16_SWIGLU``).  Derived from the always-fresh
+    concatenated shadow; rebuilt only when the parameters may have changed."""
+    key = (kernels.param_epoch, w1._version, w3._version, w1.data_ptr(), w3.data_ptr())
+    ent = getattr(w1, "_b200_gate_shadow", None)
+    if ent is None or ent[0] != key:
+        ws = weight_shadow((w1, w3))  # [2F, K]: rows 0..F-1 = w1, F..2F-1 = w3
+        F_ = w1.shape[0]
+        buf = ent[1] if ent is not None and ent[1].shape == ws.shape and ent[1].device == ws.device \
+            else torch.empty_like(ws)
+        buf.view(F_, 2, -1).copy_(ws.view(2, F_, -1).transpose(0, 1))
+        ent = (key, buf)
+        w1._b200_gate_shadow = ent
+    return ent[1]
+
+
+def swiglu_linear_nograd(x: Tensor, w1: Tensor, w3: Tensor) -> Tensor:
+    """``silu(x w1ᵀ) * (x w3ᵀ)`` as ONE GEMM with the gate in its epilogue.  Nothing is saved for
+    backward, so this is the serving / evaluation path (``torch.no_grad()``); training keeps the two-kernel form
+    because its backward needs both pre-activations."""
+    K = w1.shape[1]
+    x2 = _to_bf16_2d(x, K)
+    h = kernels.gemm(x2, gated_shadow(w1, w3), epilogue=kernels.EPI_BF16_SWIGLU)
+    return h.view(*x.shape[:-1], w1.shape[0])
+
+
 class EmbeddingFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, ids: Tensor, w: Tensor):

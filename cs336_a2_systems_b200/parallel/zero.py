@@ -175,6 +175,7 @@ class BucketFusedAdamW:
             torch.cuda.current_stream(self.device).wait_event(ev)
             self.t += 1
             self._launched = False
+            kernels.bump_param_epoch()
             # shadows that could not live in the arena (a fused group straddling a bucket edge) are re-cast lazily
             lo = self.sarena.bytes.data_ptr()
             hi = lo + self.sarena.nbytes

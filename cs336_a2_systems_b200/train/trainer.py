@@ -20,6 +20,7 @@ import torch
 from torch import Tensor
 
 from ..ops import cross_entropy, grad_slots
+from ..ops import kernels as kernels_mod
 from ..ops.api import clip_gradient
 from ..utils import nvtx
 
@@ -195,6 +196,7 @@ class Trainer:
         self._static_x.copy_(x, non_blocking=True)
         self._static_y.copy_(y, non_blocking=True)
         self._graph.replay()
+        kernels_mod.bump_param_epoch()  # the replayed optimizer kernels rewrote the parameters
         return self._static_loss
 
     def step_from_host(self, x_host: Tensor, y_host: Tensor) -> float:

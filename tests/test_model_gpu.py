@@ -113,3 +113,34 @@ def test_trainer_overlapped_optimizer_matches_plain(graph):
         torch.testing.assert_close(p, q, rtol=1e-6, atol=1e-7, msg=n)
     tb.optimizer.sync_step_from_device()
     assert tb.optimizer.state[next(b.parameters())]["t"] == 9
+
+
+def test_no_grad_forward_uses_gated_gemm_and_tracks_updates():
+    """Under ``torch.no_grad()`` the FFN runs w1‖w3 as one GEMM with the SwiGLU gate in its epilogue (interleaved
+    weight shadow).  It must agree with the training-mode forward, also after fused optimizer steps that rewrite
+    the parameters without touching ``Tensor._version``."""
+    model = _model(layers=2)
+    opt = AdamW(model.parameters(), lr=3e-3, weight_decay=0.0)
+    x = torch.randint(0, 1000, (2, 128), device="cuda")
+    y = torch.roll(x, -1, dims=1)
+
+    def both():
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            a = model(x).float()
+            with torch.no_grad():
+                b = model(x).float()
+        return a.detach(), b
+
+    a, b = both()
+    assert _rel(b, a) < 2e-2
+    assert hasattr(model.layers[0].ffn.w1.weight, "_b200_gate_shadow")
+    before = b.clone()
+    for _ in range(3):
+        opt.zero_grad()
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            loss = cross_entropy(model(x), y)
+        loss.backward()
+        opt.step()
+    a, b = both()
+    assert _rel(b, a) < 2e-2
+    assert _rel(b, before) > 1e-3  # the eval path saw the updated weights
