@@ -51,6 +51,9 @@ def parse_args():
                          "per-bucket NVLink reduce kernel (every rank still ends the step with all updated fp32 "
                          "parameters); 'replicated' = all-reduce then full AdamW on every rank; 'auto' = sharded for "
                          "2..4 ranks (measured faster), replicated otherwise")
+    ap.add_argument("--watchdog-s", type=float, default=420.0,
+                    help="abort the whole process (exit code 3, one JSON error line) if the run has not finished "
+                         "after this many seconds, instead of sitting in a collective until its 10-minute timeout")
     ap.add_argument("--no-overlap", action="store_true",
                     help="ours: run the optimizer after backward instead of overlapping it with backward")
     return ap.parse_args()
@@ -204,8 +207,32 @@ def build_reference(args, rank, ws, dev):
     return step_device, step_e2e, None, {"launches_per_step": None}, {"sharded_optimizer": bool(args.sharded and ws > 1)}
 
 
+def _arm_watchdog(seconds: float):
+    import threading
+
+    def fire():
+        if int(os.environ.get("RANK", "0")) == 0:
+            print(json.dumps({"error": f"watchdog: bench.py still running after {seconds:.0f} s", "impl": "ours"}),
+                  flush=True)
+        os._exit(3)
+
+    t = threading.Timer(seconds, fire)
+    t.daemon = True
+    t.start()
+    return t
+
+
 def main():
     args = parse_args()
+    watchdog = _arm_watchdog(args.watchdog_s) if args.watchdog_s > 0 else None
+    try:
+        return _main(args)
+    finally:
+        if watchdog is not None:
+            watchdog.cancel()
+
+
+def _main(args):
     if args.impl == "reference":
         sys.path.insert(0, os.path.join(ROOT, "baseline"))
         import ref_loader
