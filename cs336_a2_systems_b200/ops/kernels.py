@@ -39,6 +39,13 @@ def bump_param_epoch() -> None:
     param_epoch += 1
 
 
+def native_launches() -> int:
+    """Exact number of kernels the native library has launched in this process (counted at the launch sites)."""
+    fn = _lib().b200_launch_count
+    fn.restype = ctypes.c_longlong
+    return int(fn())
+
+
 def _count(n: int = 1) -> None:
     global launches
     launches += n

@@ -35,7 +35,16 @@ const char* get_error();
     }                                                    \
   } while (0)
 
-#define B200_LAUNCH_CHECK() B200_CHECK_CUDA(cudaGetLastError())
+// Every kernel launch of the library is counted (bench.py reports the number as "gpu_launches"):
+// B200_LAUNCH_CHECK() follows each <<<>>> launch, launch_pdl() counts its own.
+void count_launch(int n = 1);
+long long launch_count();
+
+#define B200_LAUNCH_CHECK()                  \
+  do {                                       \
+    ::b200::count_launch();                  \
+    B200_CHECK_CUDA(cudaGetLastError());     \
+  } while (0)
 
 // Launch with the programmatic-stream-serialization attribute (PDL): the kernel may begin while its predecessor
 // drains; kernels order themselves with griddepcontrol.wait.  B200SYS_PDL=0 falls back to plain launches.
@@ -53,6 +62,7 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  count_launch();
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 

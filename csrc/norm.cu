@@ -283,7 +283,7 @@ extern "C" int b200_rmsnorm_fwd(const void* x, int x_dtype, const void* resid_bf
   else if (x_dtype == B200_BF16 && y_dtype == B200_F32) LAUNCH(__nv_bfloat16, float);
   else { set_error("rmsnorm_fwd: bad dtypes %d -> %d", x_dtype, y_dtype); return B200_ERR_ARG; }
 #undef LAUNCH
-  B200_LAUNCH_CHECK();
+  B200_CHECK_CUDA(cudaGetLastError());  // launch_pdl counted the launch
   return 0;
 }
 
@@ -322,7 +322,7 @@ extern "C" int b200_rmsnorm_bwd(const void* dy, int dy_dtype, const float* x, co
     else BY_DT_W(6);
 #undef BY_DT_W
 #undef LAUNCH_W
-    B200_LAUNCH_CHECK();
+    B200_CHECK_CUDA(cudaGetLastError());  // launch_pdl counted the launch
     {
       dim3 g2(ceil_div(d >> 2, 128), chunks);
       if (dy_dtype == B200_BF16)

@@ -2,6 +2,7 @@
 #include "common.cuh"
 #include "tensormap.h"
 
+#include <atomic>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -17,6 +18,10 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 const char* get_error() { return g_err; }
+
+static std::atomic<long long> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+long long launch_count() { return g_launches.load(std::memory_order_relaxed); }
 
 bool pdl_enabled() {
   static int v = -1;
@@ -90,6 +95,8 @@ extern "C" {
 const char* b200_last_error(void) { return b200::get_error(); }
 
 int b200_version(void) { return 100; }
+
+long long b200_launch_count(void) { return b200::launch_count(); }
 
 int b200_device_info(int* sm_count, int* cc_major, int* cc_minor) {
   int dev = 0;

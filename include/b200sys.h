@@ -20,6 +20,8 @@ enum { B200_BF16 = 0, B200_F32 = 1 };
 
 const char* b200_last_error(void);
 int b200_version(void);
+/* kernels launched by this library in this process so far (every entry point counts its own launches) */
+long long b200_launch_count(void);
 int b200_device_info(int* sm_count, int* cc_major, int* cc_minor);
 
 /* ---- tcgen05 GEMM --------------------------------------------------------------------------
