@@ -1,4 +1,6 @@
-"""Worker bodies for the 2-process gloo DDP / sharded-optimizer tests (spawned with mp.spawn)."""
+"""Worker bodies for the 2-process gloo DDP / sharded-optimizer tests (spawned with mp.spawn);
+protocols of the reference's ``tests/test_ddp.py:29-181``, ``test_ddp_individual_parameters.py:39-161`` and
+``test_sharded_optimizer.py:29-85``."""
 from __future__ import annotations
 
 import copy

@@ -1,6 +1,6 @@
 """Shared helpers for the distributed tests: toy models, process-group setup, equivalence checks.
 
-Same protocol as the reference's ``tests/common.py`` (2-process gloo runs checked against a
+Same protocol as the reference's ``tests/common.py:13-94`` (2-process gloo runs checked against a
 single-process model trained on the full batch); data is generated from a fixed seed instead of
 being loaded from fixture files.
 """

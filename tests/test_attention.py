@@ -1,4 +1,5 @@
-"""FlashAttention-2 Functions vs. a materialised-softmax oracle (reference tests/test_attention.py)."""
+"""FlashAttention-2 Functions vs. a materialised-softmax oracle (reference ``tests/test_attention.py:11-104``:
+same inputs B=4, N=128, D=64, seed 0, same oracle, same 1e-2 tolerances, logsumexp found among the saved tensors)."""
 import pytest
 import torch
 

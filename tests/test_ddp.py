@@ -1,4 +1,4 @@
-"""Bucketed overlapped DDP == single-process training (reference tests/test_ddp.py).
+"""Bucketed overlapped DDP == single-process training (reference ``tests/test_ddp.py:29-181``).
 
 Bucket sizes are chosen so the toy models split into two buckets, one bucket per parameter, and a
 single bucket.

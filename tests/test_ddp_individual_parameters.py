@@ -1,4 +1,6 @@
-"""Per-parameter overlapped DDP == single-process training (reference tests/test_ddp_individual_parameters.py)."""
+"""Per-parameter overlapped DDP == single-process training (reference
+``tests/test_ddp_individual_parameters.py:28-161``: 2-process gloo, rank-seeded replicas equalised by the wrapper, 5 SGD steps
+on disjoint shards vs one model on the full batch)."""
 import pytest
 import torch.multiprocessing as mp
 

@@ -1,4 +1,5 @@
-"""Sharded optimizer == plain optimizer to default numpy tolerance (reference tests/test_sharded_optimizer.py)."""
+"""Sharded optimizer == plain optimizer to default numpy tolerance (reference
+``tests/test_sharded_optimizer.py:18-85``: torch.optim.AdamW plain vs sharded, 10 steps, ``assert_allclose`` at rtol 1e-7)."""
 import pytest
 import torch.multiprocessing as mp
 
