@@ -136,3 +136,17 @@ def test_lm_forward_backward_snapshot(array_snapshot):
         "logits": logits, "loss": loss,
         "grad_q0": m.layers[0].attn.q_proj.weight.grad, "grad_ln_final": m.ln_final.weight.grad,
     }, rtol=1e-4, atol=1e-5)
+
+
+def test_reference_names_resolve():
+    """``compat`` exposes the reference's public names as aliases of the native objects."""
+    import cs336_a2_systems_b200.compat as compat
+    from cs336_a2_systems_b200.ops import FlashAttentionSM100
+    from cs336_a2_systems_b200.parallel import DDPBucketed, DDPIndividualParameters, ShardedOptimizer
+
+    for name in compat.__all__:
+        assert hasattr(compat, name), name
+    assert compat.BasicsTransformerLM is TransformerLM
+    assert compat.FlashAttentionTriton is FlashAttentionSM100
+    assert compat.DDP is DDPIndividualParameters and compat.DDP_Bucketed is DDPBucketed
+    assert compat.ShardedStateOptimizer is ShardedOptimizer
