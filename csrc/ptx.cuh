@@ -64,6 +64,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 // launch_dependents: the next kernel in the stream may start being scheduled (its prologue overlaps our tail);
 // wait: blocks until the preceding kernel has completed and its memory is visible — every kernel calls it before
 // touching global memory, so only set-up work (barrier init, TMEM allocation, descriptor prefetch) ever overlaps.
+// named barrier among `nthreads` threads of the CTA (ids 1..15; 0 is __syncthreads)
+__device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
 __device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 

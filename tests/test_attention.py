@@ -78,3 +78,36 @@ def test_flash_sm100_shapes_bf16(N, D, is_causal):
     f = get_flashattention_autograd_function_triton().apply
     _check_forward(f, "cuda", is_causal, tol=2e-2, B=2, N=N, D=D, dtype=torch.bfloat16)
     _check_backward(f, "cuda", is_causal, tol=3e-2, B=2, N=N, D=D, dtype=torch.bfloat16)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(__import__("os").environ.get("B200SYS_TEST_EXPERIMENTAL") != "1",
+                    reason="opt-in: kernels not yet validated on hardware (set B200SYS_TEST_EXPERIMENTAL=1)")
+def test_flash_forward_two_warpgroup_variant_matches_default():
+    """The opt-in forward kernel with two softmax warpgroups per CTA (B200SYS_FA_FWD_WG2=1, read once per process,
+    hence the subprocess) must reproduce the default kernel's O and logsumexp."""
+    import os
+    import subprocess
+    import sys
+
+    code = r'''
+import os
+import torch
+from cs336_a2_systems_b200.ops import kernels as k
+torch.manual_seed(0)
+for (B, H, N, D, causal) in [(2, 3, 512, 64, True), (1, 2, 1000, 64, False), (1, 2, 384, 128, True), (1, 1, 300, 16, True)]:
+    q, kk, v = (torch.randn(B, H, N, D, device="cuda").bfloat16() for _ in range(3))
+    o, lse = k.fa2_fwd(q, kk, v, causal)
+    torch.save((o.float().cpu(), lse.cpu()), os.environ["FA_OUT"] + f"_{B}_{H}_{N}_{D}.pt")
+'''
+    import tempfile
+    with tempfile.TemporaryDirectory() as tmp:
+        outs = {}
+        for tag, env in (("base", "0"), ("wg2", "1")):
+            e = dict(os.environ, B200SYS_FA_FWD_WG2=env, FA_OUT=os.path.join(tmp, tag))
+            subprocess.run([sys.executable, "-c", code], check=True, env=e, timeout=120,
+                           cwd=os.path.dirname(os.path.dirname(__file__)))
+            outs[tag] = {f: torch.load(os.path.join(tmp, f)) for f in sorted(os.listdir(tmp)) if f.startswith(tag)}
+        for (fa, (oa, la)), (fb, (ob, lb)) in zip(sorted(outs["base"].items()), sorted(outs["wg2"].items())):
+            torch.testing.assert_close(ob, oa, rtol=2e-2, atol=2e-2, msg=fb)
+            torch.testing.assert_close(lb, la, rtol=1e-3, atol=1e-3, msg=fb)
