@@ -90,3 +90,21 @@ def claim_group(params) -> torch.Tensor | None:
     for s in slots:
         s.claimed = True
     return base.narrow(0, off0, rows * cols).view(rows, cols)
+
+
+def fusion_friendly_order(model) -> list:
+    """Parameters of ``model`` in an order where the members of every fused GEMM group are adjacent: q/k/v already
+    are (registration order); for SwiGLU blocks (``w1, w2, w3``) the up-projection ``w3`` is moved next to the gate
+    ``w1`` so that :func:`claim_group` can hand the fused w1‖w3 wgrad GEMM one joint slot."""
+    params = list(model.parameters())
+    pos = {id(p): i for i, p in enumerate(params)}
+    for m in model.modules():
+        w1, w2, w3 = (getattr(getattr(m, n, None), "weight", None) for n in ("w1", "w2", "w3"))
+        if w1 is None or w2 is None or w3 is None:
+            continue
+        i1, i2, i3 = pos.get(id(w1)), pos.get(id(w2)), pos.get(id(w3))
+        if i1 is None or i2 is None or i3 is None or not (i2 == i1 + 1 and i3 == i2 + 1):
+            continue
+        params[i2], params[i3] = w3, w2
+        pos[id(w3)], pos[id(w2)] = i2, i3
+    return params

@@ -15,6 +15,7 @@ stays exact (see ``optim/adamw.py``).
 from __future__ import annotations
 
 import contextlib
+import os
 
 import torch
 from torch import Tensor
@@ -130,7 +131,9 @@ class Trainer:
                              "it cannot be combined with global gradient-norm clipping")
         self.arena = None
         if grad_arena or (grad_arena is None and self.device.type == "cuda" and not self._is_ddp):
-            self.arena = GradArena(list(model.parameters()))
+            # opt-in (not yet timed on hardware): lay w3's slot next to w1's so their wgrads become ONE GEMM
+            fuse_w13 = os.environ.get("B200SYS_FUSE_W13_WGRAD", "0") == "1"
+            self.arena = GradArena(grad_slots.fusion_friendly_order(model) if fuse_w13 else list(model.parameters()))
         self._overlap = None
         if overlap_optimizer and self.device.type == "cuda" and max_grad_norm is None and \
                 hasattr(optimizer, "step_subset"):

@@ -150,3 +150,16 @@ def test_reference_names_resolve():
     assert compat.FlashAttentionTriton is FlashAttentionSM100
     assert compat.DDP is DDPIndividualParameters and compat.DDP_Bucketed is DDPBucketed
     assert compat.ShardedStateOptimizer is ShardedOptimizer
+
+
+def test_fusion_friendly_parameter_order():
+    from cs336_a2_systems_b200.ops import grad_slots
+
+    m = TransformerLM(vocab_size=32, context_length=8, d_model=16, num_layers=2, num_heads=2, d_ff=32)
+    order = grad_slots.fusion_friendly_order(m)
+    assert sorted(map(id, order)) == sorted(map(id, m.parameters()))  # a permutation
+    idx = {id(p): i for i, p in enumerate(order)}
+    for blk in m.layers:
+        assert idx[id(blk.ffn.w3.weight)] == idx[id(blk.ffn.w1.weight)] + 1
+        a = blk.attn
+        assert idx[id(a.k_proj.weight)] == idx[id(a.q_proj.weight)] + 1 == idx[id(a.v_proj.weight)] - 1
