@@ -35,6 +35,20 @@ const char* get_error();
     }                                                    \
   } while (0)
 
+// Opt a kernel into more than 48 KB of dynamic shared memory, once per (launch site, device): the attribute is a
+// per-device property, so a process that drives several GPUs must set it on each of them.
+#define B200_ENSURE_DYN_SMEM(kern, bytes)                                                              \
+  do {                                                                                                 \
+    static unsigned long long _done_mask = 0ull; /* one bit per device ordinal (mod 64) */             \
+    int _dev = 0;                                                                                      \
+    B200_CHECK_CUDA(cudaGetDevice(&_dev));                                                             \
+    const unsigned long long _bit = 1ull << (_dev & 63);                                               \
+    if (!(_done_mask & _bit)) {                                                                        \
+      B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes))); \
+      _done_mask |= _bit;                                                                              \
+    }                                                                                                  \
+  } while (0)
+
 // Every kernel launch of the library is counted (bench.py reports the number as "gpu_launches"):
 // B200_LAUNCH_CHECK() follows each <<<>>> launch, launch_pdl() counts its own.
 void count_launch(int n = 1);

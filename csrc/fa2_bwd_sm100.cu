@@ -770,11 +770,7 @@ static int launch_bwd(const CUtensorMap& q, const CUtensorMap& k, const CUtensor
                       const BwdParams& p, int B, cudaStream_t s) {
   using C = BwdCfg<DP>;
   auto kern = fa2_bwd_kernel<DP>;
-  static bool configured = false;
-  if (!configured) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-    configured = true;
-  }
+  B200_ENSURE_DYN_SMEM(kern, C::SMEM_BYTES);
   dim3 grid(ceil_div(p.Nk, BN), p.H, B);
   B200_CHECK_CUDA(launch_pdl(kern, grid, dim3(kThreads), C::SMEM_BYTES, s, q, k, v, dO, p));
   return 0;
@@ -785,11 +781,7 @@ static int launch_bwd_wg(const CUtensorMap& q, const CUtensorMap& k, const CUten
                          const BwdParams& p, int B, cudaStream_t s) {
   using C = BwdCfg<DP>;
   auto kern = fa2_bwd_wg_kernel<DP, NG>;
-  static bool configured = false;
-  if (!configured) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-    configured = true;
-  }
+  B200_ENSURE_DYN_SMEM(kern, C::SMEM_BYTES);
   dim3 grid(ceil_div(p.Nk, BN), p.H, B);
   B200_CHECK_CUDA(launch_pdl(kern, grid, dim3(NG * 128 + 64), C::SMEM_BYTES, s, q, k, v, dO, p));
   return 0;

@@ -609,11 +609,7 @@ static int launch_fwd(const CUtensorMap& q, const CUtensorMap& k, const CUtensor
                       cudaStream_t s) {
   using C = FwdCfg<DP>;
   auto kern = fa2_fwd_kernel<DP>;
-  static bool configured = false;
-  if (!configured) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-    configured = true;
-  }
+  B200_ENSURE_DYN_SMEM(kern, C::SMEM_BYTES);
   dim3 grid(p.num_m_tiles, p.H, B);
   B200_CHECK_CUDA(launch_pdl(kern, grid, dim3(kThreads), C::SMEM_BYTES, s, q, k, v, p));
   return 0;
@@ -624,11 +620,7 @@ static int launch_fwd_wg2(const CUtensorMap& q, const CUtensorMap& k, const CUte
                           cudaStream_t s) {
   using C = Fwd2Cfg<DP>;
   auto kern = fa2_fwd_wg2_kernel<DP>;
-  static bool configured = false;
-  if (!configured) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-    configured = true;
-  }
+  B200_ENSURE_DYN_SMEM(kern, C::SMEM_BYTES);
   dim3 grid(p.num_m_tiles, p.H, B);
   B200_CHECK_CUDA(launch_pdl(kern, grid, dim3(kThreads2), C::SMEM_BYTES, s, q, k, v, p));
   return 0;

@@ -210,11 +210,7 @@ template <int BN, bool A_MN, bool B_MN, int EPI>
 static int launch2(const CUtensorMap& tmA, const CUtensorMap& tmB, const Params& p, cudaStream_t stream) {
   using C = Cfg2<BN>;
   auto kern = gemm2_bf16_kernel<BN, A_MN, B_MN, EPI>;
-  static bool configured = false;
-  if (!configured) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-    configured = true;
-  }
+  B200_ENSURE_DYN_SMEM(kern, C::SMEM_BYTES);
   const int tiles = ceil_div(p.num_m, 2) * p.num_n;
   const int clusters = num_sms() / 2;
   const int grid = 2 * (tiles < clusters ? tiles : clusters);

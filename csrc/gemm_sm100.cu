@@ -207,11 +207,7 @@ template <int BN, bool A_MN, bool B_MN, int EPI>
 static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Params& p, cudaStream_t stream) {
   using C = Cfg<BN>;
   auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, EPI>;
-  static bool configured = false;  // per instantiation
-  if (!configured) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-    configured = true;
-  }
+  B200_ENSURE_DYN_SMEM(kern, C::SMEM_BYTES);
   const int tiles = p.num_m * p.num_n;
   const int grid = tiles < num_sms() ? tiles : num_sms();
   B200_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kThreads), C::SMEM_BYTES, stream, tmA, tmB, p));
