@@ -3,7 +3,7 @@ the 16x16384x64 causal shape.  The variants are selected by environment variable
 process, so set them on the command line:
 
     python tools/fa_variants_check.py                                  # default kernels
-    B200SYS_FA_FWD_WG2=1 python tools/fa_variants_check.py             # forward, two softmax warpgroups
+    B200SYS_FA_FWD_WG2=1 python tools/fa_variants_check.py             # forward, two softmax warpgroups (2: + O in TMEM)
     B200SYS_FA_BWD_WG=2 python tools/fa_variants_check.py              # backward, 2 (or 4) softmax column groups
 """
 import os
