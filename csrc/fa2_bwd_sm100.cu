@@ -696,6 +696,359 @@ fa2_bwd_wg_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
   }
 }
 
+// Same column split, with the tensor-core work re-ordered so that it overlaps the softmax warps (head dim <= 64 only,
+// opt-in: B200SYS_FA_BWD_WG=2r / 4r): after P_it / dS_it are published the MMA warp issues S and dP of tile it+1 BEFORE
+// dV, dK, dQ of tile it; the softmax warps turn S/dP(it+1) into packed P/dS registers while those three GEMMs run,
+// and only wait for them (dq_full) before overwriting the shared P / dS tiles; the dQ partial of tile it is drained
+// after P/dS(it+1) have been published.
+template <int DP, int NG>
+__global__ void __launch_bounds__(NG * 128 + 64, 1)
+fa2_bwd_wgr_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                  const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
+                  const BwdParams p) {
+  using C = BwdCfg<DP>;
+  constexpr int TMA_WARP = NG * 4, MMA_WARP = NG * 4 + 1;
+  constexpr int SC = BN / NG;              // S / dP columns per group
+  constexpr int QC = DP / NG;              // dQ / dK / dV columns per group
+  constexpr int W = QC >= 32 ? 32 : 16;    // TMEM chunk width for the dQ / dK / dV columns
+  static_assert(SC % 32 == 0 && QC % W == 0, "column split");
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sK = smem;
+  uint8_t* sV = sK + C::TILE_BYTES;
+  uint8_t* sStage = sV + C::TILE_BYTES;
+  uint8_t* sP = sStage + C::STAGES * 2 * C::TILE_BYTES;
+  uint8_t* sdS = sP + C::PS_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sdS + C::PS_BYTES);
+  uint64_t* kv_full = bars;
+  uint64_t* qdo_full = bars + 1;
+  uint64_t* qdo_empty = qdo_full + C::STAGES;
+  uint64_t* sdp_full = qdo_empty + C::STAGES;
+  uint64_t* pds_full = sdp_full + 1;
+  uint64_t* dq_full = pds_full + 1;
+  uint64_t* dq_empty = dq_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(dq_empty + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int j = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int kv0 = j * BN;
+  const int i_start = p.causal ? (kv0 / BM) : 0;
+  const int n_iter = max(0, p.num_q_tiles - i_start);
+
+  if (warp == TMA_WARP && ptx::elect_one()) {
+    ptx::tma_prefetch_desc(&tmQ);
+    ptx::tma_prefetch_desc(&tmK);
+    ptx::tma_prefetch_desc(&tmV);
+    ptx::tma_prefetch_desc(&tmdO);
+    ptx::mbar_init(kv_full, 1);
+    for (int s = 0; s < C::STAGES; ++s) {
+      ptx::mbar_init(&qdo_full[s], 1);
+      ptx::mbar_init(&qdo_empty[s], 1);
+    }
+    ptx::mbar_init(sdp_full, 1);
+    ptx::mbar_init(pds_full, 4 * NG);  // one arrive per softmax warp
+    ptx::mbar_init(dq_full, 1);
+    ptx::mbar_init(dq_empty, 4 * NG);
+    ptx::fence_mbar_init();
+  }
+  if (warp == MMA_WARP) {
+    ptx::tmem_alloc(tmem_slot, C::TMEM_COLS);
+    ptx::tmem_relinquish();
+  }
+  ptx::griddep_launch();
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  ptx::griddep_wait();
+
+  if (warp == TMA_WARP) {
+    // ===================================== TMA producer =====================================
+    if (ptx::elect_one() && n_iter > 0) {
+      ptx::mbar_expect_tx(kv_full, 2 * C::TILE_BYTES);
+#pragma unroll
+      for (int blk = 0; blk < C::NBLK; ++blk) {
+        ptx::tma_load_4d(sK + blk * (BN * 128), &tmK, kv_full, blk * 64, kv0, h, b, ptx::kEvictFirst);
+        ptx::tma_load_4d(sV + blk * (BN * 128), &tmV, kv_full, blk * 64, kv0, h, b, ptx::kEvictFirst);
+      }
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int it = 0; it < n_iter; ++it) {
+        const int q0 = (i_start + it) * BM;
+        ptx::mbar_wait(&qdo_empty[stage], phase ^ 1);
+        ptx::mbar_expect_tx(&qdo_full[stage], 2 * C::TILE_BYTES);
+        uint8_t* dq_ = sStage + stage * 2 * C::TILE_BYTES;
+        uint8_t* ddo = dq_ + C::TILE_BYTES;
+#pragma unroll
+        for (int blk = 0; blk < C::NBLK; ++blk) {
+          ptx::tma_load_4d(dq_ + blk * (BM * 128), &tmQ, &qdo_full[stage], blk * 64, q0, h, b, ptx::kEvictLast);
+          ptx::tma_load_4d(ddo + blk * (BM * 128), &tmdO, &qdo_full[stage], blk * 64, q0, h, b, ptx::kEvictLast);
+        }
+        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == MMA_WARP) {
+    // ===================================== MMA issuer =====================================
+    if (ptx::elect_one() && n_iter > 0) {
+      constexpr uint32_t idesc_s = ptx::make_idesc(BM, BN, false, false);
+      constexpr uint32_t idesc_dkv = ptx::make_idesc(BN, DP, true, true);
+      constexpr uint32_t idesc_dq = ptx::make_idesc(BM, DP, false, true);
+      const uint32_t k_addr = ptx::smem_u32(sK), v_addr = ptx::smem_u32(sV);
+      const uint32_t p_addr = ptx::smem_u32(sP), ds_addr = ptx::smem_u32(sdS);
+      const uint32_t st_addr = ptx::smem_u32(sStage);
+      ptx::mbar_wait(kv_full, 0);
+      // S and dP of tile `t` from stage t % STAGES (the stage's n-th use has parity n & 1)
+      auto issue_sdp = [&](int t) {
+        const int st = t % C::STAGES;
+        const uint32_t q_addr = st_addr + st * 2 * C::TILE_BYTES;
+        const uint32_t do_addr = q_addr + C::TILE_BYTES;
+        ptx::mbar_wait(&qdo_full[st], (uint32_t)((t / C::STAGES) & 1));
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < DP / 16; ++kk) {
+          const uint32_t off = (kk >> 2) * (128 * 128) + (kk & 3) * 32;
+          ptx::mma_f16_ss(tmem_base + C::COL_S, ptx::make_smem_desc(q_addr + off, 16, 1024),
+                          ptx::make_smem_desc(k_addr + off, 16, 1024), idesc_s, kk != 0);
+        }
+#pragma unroll
+        for (int kk = 0; kk < DP / 16; ++kk) {
+          const uint32_t off = (kk >> 2) * (128 * 128) + (kk & 3) * 32;
+          ptx::mma_f16_ss(tmem_base + C::COL_DP, ptx::make_smem_desc(do_addr + off, 16, 1024),
+                          ptx::make_smem_desc(v_addr + off, 16, 1024), idesc_s, kk != 0);
+        }
+        ptx::mma_commit(sdp_full);
+      };
+      issue_sdp(0);
+      for (int it = 0; it < n_iter; ++it) {
+        const int st = it % C::STAGES;
+        const uint32_t q_addr = st_addr + st * 2 * C::TILE_BYTES;
+        const uint32_t do_addr = q_addr + C::TILE_BYTES;
+        ptx::mbar_wait(pds_full, it & 1);  // P_it, dS_it in smem; S_it / dP_it fully read out of tensor memory
+        ptx::tc_fence_after();
+        // next tile's S / dP first: the softmax warps work on them while dV, dK, dQ of this tile run
+        if (it + 1 < n_iter) issue_sdp(it + 1);
+#pragma unroll
+        for (int kk = 0; kk < BM / 16; ++kk) {
+          const uint32_t acc = (it > 0 || kk > 0) ? 1u : 0u;
+          ptx::mma_f16_ss(tmem_base + C::COL_DV, ptx::make_smem_desc(p_addr + kk * 2048, BM * 128, 1024),
+                          ptx::make_smem_desc(do_addr + kk * 2048, BM * 128, 1024), idesc_dkv, acc);
+        }
+#pragma unroll
+        for (int kk = 0; kk < BM / 16; ++kk) {
+          const uint32_t acc = (it > 0 || kk > 0) ? 1u : 0u;
+          ptx::mma_f16_ss(tmem_base + C::COL_DK, ptx::make_smem_desc(ds_addr + kk * 2048, BM * 128, 1024),
+                          ptx::make_smem_desc(q_addr + kk * 2048, BM * 128, 1024), idesc_dkv, acc);
+        }
+        if (it > 0) {
+          ptx::mbar_wait(dq_empty, (it - 1) & 1);  // the previous dQ partial has been drained
+          ptx::tc_fence_after();
+        }
+#pragma unroll
+        for (int kk = 0; kk < BN / 16; ++kk) {
+          const uint32_t a_off = (kk >> 2) * (BM * 128) + (kk & 3) * 32;
+          ptx::mma_f16_ss(tmem_base + C::COL_DQ, ptx::make_smem_desc(ds_addr + a_off, 16, 1024),
+                          ptx::make_smem_desc(k_addr + kk * 2048, BN * 128, 1024), idesc_dq, kk != 0);
+        }
+        ptx::mma_commit(&qdo_empty[st]);
+        ptx::mma_commit(dq_full);
+      }
+    }
+  } else {
+    // ===================================== NG softmax / dS warpgroups =====================================
+    const int wq = warp & 3;    // TMEM lane quadrant
+    const int grp = warp >> 2;  // column group
+    const int r = wq * 32 + lane;
+    const uint32_t lane_base = static_cast<uint32_t>(wq * 32) << 16;
+    const long long bh = (long long)b * p.H + h;
+    float lse_next = 0.f, dl_next = 0.f;
+    if (n_iter > 0) {
+      const int row0 = i_start * BM + r;
+      if (row0 < p.Nq) { lse_next = p.lse[bh * p.Nq + row0]; dl_next = p.delta[bh * p.Nq + row0]; }
+    }
+    // fp32 red.add of this group's columns of a dQ partial (query row `qrow`) into the accumulator
+    auto drain_dq = [&](int qrow, int it_done) {
+      (void)it_done;
+      const bool ok = qrow < p.Nq;
+      float* dq_row = p.dq_acc + (bh * p.Nq + qrow) * (long long)p.D;
+#pragma unroll
+      for (int cc = 0; cc < QC / W; ++cc) {
+        const int col0 = grp * QC + cc * W;
+        uint32_t t[W];
+        tmem_ld_cols<W>(tmem_base + C::COL_DQ + lane_base + col0, t);
+        ptx::tmem_ld_wait();
+        if (ok) {
+          if ((p.D & 3) == 0) {
+#pragma unroll
+            for (int v = 0; v < W / 4; ++v) {
+              const int col = col0 + v * 4;
+              if (col < p.D)
+                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dq_row + col),
+                             "f"(__uint_as_float(t[4 * v + 0])), "f"(__uint_as_float(t[4 * v + 1])),
+                             "f"(__uint_as_float(t[4 * v + 2])), "f"(__uint_as_float(t[4 * v + 3]))
+                             : "memory");
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < W; ++i)
+              if (col0 + i < p.D) atomicAdd(dq_row + col0 + i, __uint_as_float(t[i]));
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(dq_empty);
+    };
+    for (int it = 0; it < n_iter; ++it) {
+      const int q0 = (i_start + it) * BM;
+      const int row = q0 + r;
+      const bool row_ok = row < p.Nq;
+      const float L2 = row_ok ? lse_next * kLog2e : 0.f;
+      const float dl = row_ok ? dl_next : 0.f;
+      if (it + 1 < n_iter && row + BM < p.Nq) {
+        lse_next = p.lse[bh * p.Nq + row + BM];
+        dl_next = p.delta[bh * p.Nq + row + BM];
+      }
+      const bool need_mask = (kv0 + BN > p.Nk) || (p.causal && kv0 + BN - 1 > q0);
+      ptx::mbar_wait(sdp_full, it & 1);
+      ptx::tc_fence_after();
+      int lim = p.Nk - kv0;
+      if (p.causal) lim = min(lim, row - kv0 + 1);
+      if (!row_ok) lim = 0;
+      // ---- P and dS of this tile into registers (packed bf16) while the previous tile's dV / dK / dQ MMAs run
+      uint32_t pk[SC / 2], dk_[SC / 2];
+#pragma unroll
+      for (int cc = 0; cc < SC / 32; ++cc) {
+        const int c = grp * (SC / 32) + cc;
+        uint32_t s[32], dp[32];
+        ptx::tmem_ld_32x32b_x32(tmem_base + C::COL_S + lane_base + c * 32, s);
+        ptx::tmem_ld_32x32b_x32(tmem_base + C::COL_DP + lane_base + c * 32, dp);
+        ptx::tmem_ld_wait();
+        const bool whole = (!need_mask && row_ok) || lim >= (c + 1) * 32;
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          float e[8], d[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) e[i] = exp2f(fmaf(__uint_as_float(s[8 * v + i]), p.scale_log2, -L2));
+          if (!whole) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) e[i] = (c * 32 + 8 * v + i < lim) ? e[i] : 0.f;
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) d[i] = e[i] * (__uint_as_float(dp[8 * v + i]) - dl) * p.scale;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            pk[cc * 16 + v * 4 + i] = pack_bf16x2(e[2 * i], e[2 * i + 1]);
+            dk_[cc * 16 + v * 4 + i] = pack_bf16x2(d[2 * i], d[2 * i + 1]);
+          }
+        }
+      }
+      // ---- the P / dS tiles in shared memory are free once the previous tile's dQ MMA (their last reader) is done
+      if (it > 0) {
+        ptx::mbar_wait(dq_full, (it - 1) & 1);
+        ptx::tc_fence_after();
+      }
+#pragma unroll
+      for (int cc = 0; cc < SC / 32; ++cc) {
+        const int c = grp * (SC / 32) + cc;
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          const uint32_t off = swz_off_b(r, c * 32 + v * 8, BM);
+          *reinterpret_cast<u32x4*>(sP + off) = u32x4{pk[cc * 16 + v * 4 + 0], pk[cc * 16 + v * 4 + 1],
+                                                       pk[cc * 16 + v * 4 + 2], pk[cc * 16 + v * 4 + 3]};
+          *reinterpret_cast<u32x4*>(sdS + off) = u32x4{dk_[cc * 16 + v * 4 + 0], dk_[cc * 16 + v * 4 + 1],
+                                                        dk_[cc * 16 + v * 4 + 2], dk_[cc * 16 + v * 4 + 3]};
+        }
+      }
+      ptx::tc_fence_before();
+      ptx::fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(pds_full);
+      // ---- drain the PREVIOUS tile's dQ partial (its MMA finished: dq_full(it-1) was observed above)
+      if (it > 0) {
+        drain_dq(row - BM, it - 1);
+      }
+    }
+    if (n_iter > 0) {  // the last tile's dQ partial
+      ptx::mbar_wait(dq_full, (n_iter - 1) & 1);
+      ptx::tc_fence_after();
+      drain_dq((i_start + n_iter - 1) * BM + r, n_iter - 1);
+    }
+
+    // ---- epilogue: this group's columns of dK_j and dV_j (row r of the tile = key kv0 + r)
+    const int key = kv0 + r;
+    if (n_iter > 0) ptx::tc_fence_after();
+    __nv_bfloat16* dk_row = p.dk + (long long)b * p.dk_sb + (long long)h * p.dk_sh + (long long)key * p.dk_sr;
+    __nv_bfloat16* dv_row = p.dv + (long long)b * p.dv_sb + (long long)h * p.dv_sh + (long long)key * p.dv_sr;
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+      __nv_bfloat16* out = which == 0 ? dv_row : dk_row;
+      const uint32_t colbase = which == 0 ? C::COL_DV : C::COL_DK;
+      const bool vec = ((reinterpret_cast<uintptr_t>(out) & 15) == 0) && (p.D % 8 == 0);
+#pragma unroll
+      for (int cc = 0; cc < QC / W; ++cc) {
+        const int col0 = grp * QC + cc * W;
+        uint32_t t[W];
+        if (n_iter > 0) {
+          tmem_ld_cols<W>(tmem_base + colbase + lane_base + col0, t);
+          ptx::tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int i = 0; i < W; ++i) t[i] = 0u;
+        }
+        if (which == 1 && p.rope_epilogue && key < p.Nk) {
+          // rotate the pairs of this chunk back by -angle(position = key index): W/2 contiguous angles
+          const int half = p.D >> 1;
+          const float* cosr = p.rope_cache + (size_t)key * half + (col0 >> 1);
+          const float* sinr = p.rope_cache + (size_t)p.rope_ctx * half + (size_t)key * half + (col0 >> 1);
+          f32x4 cs[W / 8], sn[W / 8];
+#pragma unroll
+          for (int q = 0; q < W / 8; ++q) {
+            cs[q] = *reinterpret_cast<const f32x4*>(cosr + 4 * q);
+            sn[q] = *reinterpret_cast<const f32x4*>(sinr + 4 * q);
+          }
+#pragma unroll
+          for (int q = 0; q < W / 8; ++q) {
+            const float c4[4] = {cs[q].x, cs[q].y, cs[q].z, cs[q].w}, s4[4] = {sn[q].x, sn[q].y, sn[q].z, sn[q].w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int i = 4 * q + e;
+              const float a = __uint_as_float(t[2 * i]), bb = __uint_as_float(t[2 * i + 1]);
+              t[2 * i] = __float_as_uint(c4[e] * a + s4[e] * bb);
+              t[2 * i + 1] = __float_as_uint(c4[e] * bb - s4[e] * a);
+            }
+          }
+        }
+        if (key < p.Nk) {
+          if (vec) {
+#pragma unroll
+            for (int v = 0; v < W / 8; ++v) {
+              if (col0 + v * 8 < p.D) {
+                u32x4 o;
+                o.x = pack_bf16x2(__uint_as_float(t[8 * v + 0]), __uint_as_float(t[8 * v + 1]));
+                o.y = pack_bf16x2(__uint_as_float(t[8 * v + 2]), __uint_as_float(t[8 * v + 3]));
+                o.z = pack_bf16x2(__uint_as_float(t[8 * v + 4]), __uint_as_float(t[8 * v + 5]));
+                o.w = pack_bf16x2(__uint_as_float(t[8 * v + 6]), __uint_as_float(t[8 * v + 7]));
+                *reinterpret_cast<u32x4*>(out + col0 + v * 8) = o;
+              }
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < W; ++i)
+              if (col0 + i < p.D) out[col0 + i] = __float2bfloat16(__uint_as_float(t[i]));
+          }
+        }
+      }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == MMA_WARP) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, C::TMEM_COLS);
+  }
+}
+
 // delta[b,h,i] = sum_d O[b,h,i,d] * dO[b,h,i,d]; one warp per row
 __global__ void fa2_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ dout,
                                  float* __restrict__ delta, int H, int Nq, int D, long long o_sb, long long o_sh,
@@ -787,6 +1140,26 @@ static int launch_bwd_wg(const CUtensorMap& q, const CUtensorMap& k, const CUten
   return 0;
 }
 
+template <int NG>
+static int launch_bwd_wgr(const CUtensorMap& q, const CUtensorMap& k, const CUtensorMap& v, const CUtensorMap& dO,
+                          const BwdParams& p, int B, cudaStream_t s) {
+  using C = BwdCfg<64>;
+  auto kern = fa2_bwd_wgr_kernel<64, NG>;
+  B200_ENSURE_DYN_SMEM(kern, C::SMEM_BYTES);
+  dim3 grid(ceil_div(p.Nk, BN), p.H, B);
+  B200_CHECK_CUDA(launch_pdl(kern, grid, dim3(NG * 128 + 64), C::SMEM_BYTES, s, q, k, v, dO, p));
+  return 0;
+}
+
+static bool bwd_reordered() {  // B200SYS_FA_BWD_WG = "2r" / "4r"
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200SYS_FA_BWD_WG");
+    v = (e && e[0] && e[1] == 'r') ? 1 : 0;
+  }
+  return v == 1;
+}
+
 static int bwd_groups() {  // B200SYS_FA_BWD_WG: 1 (default kernel), 2 or 4 softmax column groups
   static int v = -1;
   if (v < 0) {
@@ -857,7 +1230,9 @@ extern "C" int b200_fa2_bwd_ex(const void* q, const void* k, const void* v, cons
   p.rope_cache = rope_cache; p.rope_ctx = rope_ctx;
   p.rope_epilogue = (rope_cache != nullptr && D == 64) ? 1 : 0;
   const int ng = bwd_groups();
-  if (ng == 2)
+  if (ng > 1 && bwd_reordered() && D <= 64)
+    rc = ng == 2 ? launch_bwd_wgr<2>(tq, tk, tv, tdo, p, B, s) : launch_bwd_wgr<4>(tq, tk, tv, tdo, p, B, s);
+  else if (ng == 2)
     rc = D <= 64 ? launch_bwd_wg<64, 2>(tq, tk, tv, tdo, p, B, s) : launch_bwd_wg<128, 2>(tq, tk, tv, tdo, p, B, s);
   else if (ng == 4)
     rc = D <= 64 ? launch_bwd_wg<64, 4>(tq, tk, tv, tdo, p, B, s) : launch_bwd_wg<128, 4>(tq, tk, tv, tdo, p, B, s);
