@@ -592,6 +592,294 @@ fa2_fwd_wg2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   }
 }
 
+// Two-warpgroup kernel with K/V tiles shared across a 2-CTA thread-block cluster by TMA multicast
+// (opt-in: B200SYS_FA_FWD_WG2=3; needs an even number of query tiles, else the plain two-warpgroup kernel runs).
+template <int DP>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, Fwd2Cfg<DP>::MIN_CTAS)
+fa2_fwd_wg2c_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                    const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmK64,
+                    const __grid_constant__ CUtensorMap tmV64, const FwdParams p) {
+  using C = Fwd2Cfg<DP>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sP = sQ + C::TILE_BYTES;
+  uint8_t* sKV = sP + C::P_BYTES;
+  float* xch = reinterpret_cast<float*>(sKV + C::SLOTS * C::TILE_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(xch) + C::XCH_BYTES);
+  uint64_t* q_full = bars;
+  uint64_t* kv_full = bars + 1;
+  uint64_t* kv_empty = kv_full + C::SLOTS;
+  uint64_t* s_full = kv_empty + C::SLOTS;
+  uint64_t* p_full = s_full + 1;
+  uint64_t* o_full = p_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m_tile = p.causal ? (p.num_m_tiles - 1 - (int)blockIdx.x) : (int)blockIdx.x;
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int m0 = m_tile * BM;
+
+  int n_kv = ceil_div(p.Nk, BN);
+  if (p.causal) {
+    const int lim = ceil_div(min(m0 + BM, p.Nk), BN);
+    n_kv = min(n_kv, lim);
+  }
+  // The two CTAs of a cluster work on neighbouring query tiles of the same (batch, head).  Key tiles both need
+  // (j < n_shared) are fetched cooperatively: each CTA loads one 64-row half and multicasts it into both CTAs'
+  // shared memory, halving the L2 -> SM traffic for K and V; the extra causal tile of the later query tile is
+  // loaded by its CTA alone.
+  const uint32_t cr = ptx::cluster_ctarank();
+  const int peer_bx = (int)blockIdx.x ^ 1;
+  const int peer_m0 = (p.causal ? (p.num_m_tiles - 1 - peer_bx) : peer_bx) * BM;
+  int n_kv_peer = ceil_div(p.Nk, BN);
+  if (p.causal) n_kv_peer = min(n_kv_peer, ceil_div(min(peer_m0 + BM, p.Nk), BN));
+  const int n_shared = min(n_kv, n_kv_peer);
+
+  if (warp == 8 && ptx::elect_one()) {
+    ptx::tma_prefetch_desc(&tmQ);
+    ptx::tma_prefetch_desc(&tmK);
+    ptx::tma_prefetch_desc(&tmV);
+    ptx::tma_prefetch_desc(&tmK64);
+    ptx::tma_prefetch_desc(&tmV64);
+    ptx::mbar_init(q_full, 1);
+    for (int s = 0; s < C::SLOTS; ++s) {
+      ptx::mbar_init(&kv_full[s], 1);
+      ptx::mbar_init(&kv_empty[s], 2);  // a shared slot is free when BOTH CTAs' MMAs have read it
+    }
+    ptx::mbar_init(s_full, 1);
+    ptx::mbar_init(p_full, 8);  // one arrive per softmax warp
+    ptx::mbar_init(o_full, 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 9) {
+    ptx::tmem_alloc(tmem_slot, C::TMEM_COLS);
+    ptx::tmem_relinquish();
+  }
+  ptx::griddep_launch();
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync();  // the peer's barriers are initialised before anything of ours can signal them
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  ptx::griddep_wait();
+  const uint32_t tmem_S = tmem_base;
+  const uint32_t tmem_O = tmem_base + BN;
+
+  if (warp == 8) {
+    // ===================================== TMA producer =====================================
+    if (ptx::elect_one()) {
+      ptx::mbar_expect_tx(q_full, C::TILE_BYTES);
+#pragma unroll
+      for (int blk = 0; blk < C::NBLK; ++blk)
+        ptx::tma_load_4d(sQ + blk * (BM * 128), &tmQ, q_full, blk * 64, m0, h, b, ptx::kEvictFirst);
+      int slot = 0;
+      uint32_t phase = 0;
+      for (int j = 0; j < n_kv; ++j) {
+#pragma unroll
+        for (int kv = 0; kv < 2; ++kv) {  // K_j then V_j
+          ptx::mbar_wait(&kv_empty[slot], phase ^ 1);
+          ptx::mbar_expect_tx(&kv_full[slot], C::TILE_BYTES);  // our half + the peer's half (or the whole solo tile)
+          uint8_t* dst = sKV + slot * C::TILE_BYTES;
+          if (j < n_shared) {
+#pragma unroll
+            for (int blk = 0; blk < C::NBLK; ++blk)
+              ptx::tma_load_4d_mcast(dst + blk * (BN * 128) + cr * (64 * 128), kv == 0 ? &tmK64 : &tmV64, &kv_full[slot],
+                                     blk * 64, j * BN + (int)cr * 64, h, b, (uint16_t)0x3, ptx::kEvictLast);
+          } else {
+#pragma unroll
+            for (int blk = 0; blk < C::NBLK; ++blk)
+              ptx::tma_load_4d(dst + blk * (BN * 128), kv == 0 ? &tmK : &tmV, &kv_full[slot], blk * 64, j * BN, h, b,
+                               ptx::kEvictLast);
+          }
+          if (++slot == C::SLOTS) { slot = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 9) {
+    // ===================================== MMA issuer =====================================
+    if (ptx::elect_one() && n_kv > 0) {
+      constexpr uint32_t idesc_qk = ptx::make_idesc(BM, BN, false, false);
+      constexpr uint32_t idesc_pv = ptx::make_idesc(BM, DP, false, true);
+      const uint32_t q_addr = ptx::smem_u32(sQ), p_addr = ptx::smem_u32(sP), kv_addr = ptx::smem_u32(sKV);
+      int slot = 0;
+      uint32_t phase = 0;
+      int jq = 0;  // key tile the next S = Q K^T uses
+      auto release = [&](int tile) {  // the slot just read is free in both CTAs (shared tile) or only here (solo)
+        if (tile < n_shared) ptx::mma_commit_mcast(&kv_empty[slot], (uint16_t)0x3);
+        else ptx::mma_commit(&kv_empty[slot]);
+      };
+      auto issue_qk = [&]() {
+        ptx::mbar_wait(&kv_full[slot], phase);
+        ptx::tc_fence_after();
+        const uint32_t k_addr = kv_addr + slot * C::TILE_BYTES;
+#pragma unroll
+        for (int kk = 0; kk < DP / 16; ++kk) {
+          const uint32_t off = (kk >> 2) * (BM * 128) + (kk & 3) * 32;
+          ptx::mma_f16_ss(tmem_S, ptx::make_smem_desc(q_addr + off, 16, 1024),
+                          ptx::make_smem_desc(k_addr + off, 16, 1024), idesc_qk, kk != 0);
+        }
+        release(jq++);
+        ptx::mma_commit(s_full);
+        if (++slot == C::SLOTS) { slot = 0; phase ^= 1; }
+      };
+      ptx::mbar_wait(q_full, 0);
+      issue_qk();
+      for (int j = 0; j < n_kv; ++j) {
+        ptx::mbar_wait(p_full, j & 1);  // P_j in smem; S_j and the previous PV partial fully consumed
+        ptx::tc_fence_after();
+        ptx::mbar_wait(&kv_full[slot], phase);
+        ptx::tc_fence_after();
+        const uint32_t v_addr = kv_addr + slot * C::TILE_BYTES;
+#pragma unroll
+        for (int kk = 0; kk < BN / 16; ++kk) {
+          const uint32_t a_off = (kk >> 2) * (BM * 128) + (kk & 3) * 32;
+          ptx::mma_f16_ss(tmem_O, ptx::make_smem_desc(p_addr + a_off, 16, 1024),
+                          ptx::make_smem_desc(v_addr + kk * 2048, BN * 128, 1024), idesc_pv, kk != 0);
+        }
+        release(j);
+        ptx::mma_commit(o_full);
+        if (++slot == C::SLOTS) { slot = 0; phase ^= 1; }
+        if (j + 1 < n_kv) issue_qk();
+      }
+    }
+  } else {
+    // ===================================== two softmax warpgroups =====================================
+    constexpr int OC = DP / 2;           // O columns accumulated by one half
+    const int wq = warp & 3;             // TMEM lane quadrant
+    const int half = warp >> 2;          // 0: S columns 0-63, 1: S columns 64-127
+    const int r = wq * 32 + lane;        // row within the tile == TMEM lane
+    const int row = m0 + r;
+    const uint32_t lane_base = static_cast<uint32_t>(wq * 32) << 16;
+    float o_acc[OC];
+#pragma unroll
+    for (int i = 0; i < OC; ++i) o_acc[i] = 0.f;
+    float m_run = -INFINITY, l_part = 0.f;
+
+    for (int j = 0; j < n_kv; ++j) {
+      const int kv0 = j * BN;
+      const bool need_mask = (kv0 + BN > p.Nk) || (p.causal && kv0 + BN - 1 > m0);
+      ptx::mbar_wait(s_full, j & 1);
+      ptx::tc_fence_after();
+      int lim = p.Nk - kv0;
+      if (p.causal) lim = min(lim, row - kv0 + 1);
+      // ---- pass 1: maximum over this half's 64 columns, four independent chains
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        const int c = half * 2 + cc;
+        uint32_t s[32];
+        ptx::tmem_ld_32x32b_x32(tmem_S + lane_base + c * 32, s);
+        ptx::tmem_ld_wait();
+        if (!need_mask || lim >= (c + 1) * 32) {
+#pragma unroll
+          for (int i = 0; i < 32; i += 8) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+              mx4[q] = fmaxf(mx4[q], fmaxf(__uint_as_float(s[i + 2 * q]), __uint_as_float(s[i + 2 * q + 1])));
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            mx4[i & 3] = fmaxf(mx4[i & 3], (c * 32 + i < lim) ? __uint_as_float(s[i]) : -INFINITY);
+        }
+      }
+      float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+      // ---- exchange the partial maxima of the two halves of this row
+      float* slot_x = xch + (j & 1) * (2 * BM);
+      slot_x[half * BM + r] = mx;
+      ptx::named_bar_sync(1, 256);
+      mx = fmaxf(mx, slot_x[(half ^ 1) * BM + r]);
+      const float m_new = fmaxf(m_run, mx * p.scale_log2);
+      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+      const float alpha = exp2f(m_run - m_use);
+      // ---- pass 2: P = exp2(S·scale − m) for this half's columns, partial row sum, bf16 P → swizzled smem
+      float psum = 0.f;
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        const int c = half * 2 + cc;
+        uint32_t s[32];
+        ptx::tmem_ld_32x32b_x32(tmem_S + lane_base + c * 32, s);
+        ptx::tmem_ld_wait();
+        const bool whole = !need_mask || lim >= (c + 1) * 32;
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          float e[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) e[i] = exp2f(fmaf(__uint_as_float(s[8 * v + i]), p.scale_log2, -m_use));
+          if (!whole) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) e[i] = (c * 32 + 8 * v + i < lim) ? e[i] : 0.f;
+          }
+          psum += ((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[7]));
+          u32x4 o;
+          o.x = pack_bf16x2(e[0], e[1]);
+          o.y = pack_bf16x2(e[2], e[3]);
+          o.z = pack_bf16x2(e[4], e[5]);
+          o.w = pack_bf16x2(e[6], e[7]);
+          *reinterpret_cast<u32x4*>(sP + swz_off(r, c * 32 + v * 8, BM)) = o;
+        }
+      }
+      ptx::tc_fence_before();
+      ptx::fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(p_full);
+      l_part = l_part * alpha + psum;
+      m_run = m_new;
+#pragma unroll
+      for (int i = 0; i < OC; ++i) o_acc[i] *= alpha;
+      ptx::mbar_wait(o_full, j & 1);
+      ptx::tc_fence_after();
+#pragma unroll
+      for (int c = 0; c < OC / 32; ++c) {
+        uint32_t t[32];
+        ptx::tmem_ld_32x32b_x32(tmem_O + lane_base + half * OC + c * 32, t);
+        ptx::tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o_acc[c * 32 + i] += __uint_as_float(t[i]);
+      }
+    }
+
+    // ---- epilogue: combine the two partial row sums, O / l, logsumexp
+    float* slot_x = xch + (n_kv & 1) * (2 * BM);  // the buffer NOT used by the last tile's max exchange
+    slot_x[half * BM + r] = l_part;
+    ptx::named_bar_sync(1, 256);
+    const float l_run = l_part + slot_x[(half ^ 1) * BM + r];
+    if (row < p.Nq) {
+      const float inv_l = l_run > 0.f ? 1.f / l_run : 0.f;
+      __nv_bfloat16* orow = p.o + (long long)b * p.o_sb + (long long)h * p.o_sh + (long long)row * p.o_sr + half * OC;
+      const bool vec = ((reinterpret_cast<uintptr_t>(orow) & 15) == 0) && (p.D % 8 == 0);
+      if (vec) {
+#pragma unroll
+        for (int v = 0; v < OC / 8; ++v) {
+          if (half * OC + v * 8 < p.D) {
+            u32x4 o;
+            o.x = pack_bf16x2(o_acc[8 * v + 0] * inv_l, o_acc[8 * v + 1] * inv_l);
+            o.y = pack_bf16x2(o_acc[8 * v + 2] * inv_l, o_acc[8 * v + 3] * inv_l);
+            o.z = pack_bf16x2(o_acc[8 * v + 4] * inv_l, o_acc[8 * v + 5] * inv_l);
+            o.w = pack_bf16x2(o_acc[8 * v + 6] * inv_l, o_acc[8 * v + 7] * inv_l);
+            *reinterpret_cast<u32x4*>(orow + 8 * v) = o;
+          }
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < OC; ++i)
+          if (half * OC + i < p.D) orow[i] = __float2bfloat16(o_acc[i] * inv_l);
+      }
+      if (half == 0)
+        p.lse[((long long)b * p.H + h) * p.Nq + row] = l_run > 0.f ? (m_run + log2f(l_run)) * kLn2 : -INFINITY;
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 9) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, C::TMEM_COLS);
+  }
+  ptx::cluster_sync();  // the peer may still multicast into our shared memory / signal our barriers
+}
+
 // Same two-warpgroup structure, with O resident in tensor memory and lazy rescaling (opt-in: B200SYS_FA_FWD_WG2=2).
 template <int DP>
 __global__ void __launch_bounds__(kThreads2, Fwd2Cfg<DP>::MIN_CTAS)
@@ -923,12 +1211,24 @@ static int launch_fwd_wg2o(const CUtensorMap& q, const CUtensorMap& k, const CUt
   return 0;
 }
 
-// B200SYS_FA_FWD_WG2: 0 default kernel, 1 two softmax warpgroups, 2 the same with O resident in tensor memory
+template <int DP>
+static int launch_fwd_wg2c(const CUtensorMap& q, const CUtensorMap& k, const CUtensorMap& v, const CUtensorMap& k64,
+                           const CUtensorMap& v64, const FwdParams& p, int B, cudaStream_t s) {
+  using C = Fwd2Cfg<DP>;
+  auto kern = fa2_fwd_wg2c_kernel<DP>;
+  B200_ENSURE_DYN_SMEM(kern, C::SMEM_BYTES);
+  dim3 grid(p.num_m_tiles, p.H, B);  // num_m_tiles is even: clusters of two along x
+  B200_CHECK_CUDA(launch_pdl(kern, grid, dim3(kThreads2), C::SMEM_BYTES, s, q, k, v, k64, v64, p));
+  return 0;
+}
+
+// B200SYS_FA_FWD_WG2: 0 default kernel, 1 two softmax warpgroups, 2 the same with O resident in tensor memory,
+// 3 two softmax warpgroups + K/V multicast across a 2-CTA cluster
 static int wg2_mode() {
   static int v = -1;
   if (v < 0) {
     const char* e = getenv("B200SYS_FA_FWD_WG2");
-    v = (e && (e[0] == '1' || e[0] == '2')) ? (e[0] - '0') : 0;
+    v = (e && (e[0] == '1' || e[0] == '2' || e[0] == '3')) ? (e[0] - '0') : 0;
   }
   return v;
 }
@@ -963,7 +1263,13 @@ extern "C" int b200_fa2_fwd(const void* q, const void* k, const void* v, void* o
   p.num_m_tiles = ceil_div(Nq, BM);
   p.trace = g_fa2_fwd_trace;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  if (wg2_mode() == 1)  // opt-in variant with two softmax warpgroups per CTA
+  if (wg2_mode() == 3 && (p.num_m_tiles % 2) == 0) {  // ... and K/V multicast across a CTA pair
+    CUtensorMap tk64, tv64;
+    if ((rc = make_bhnd_map(&tk64, k, B, H, Nk, D, k_strides, 64))) return rc;
+    if ((rc = make_bhnd_map(&tv64, v, B, H, Nk, D, v_strides, 64))) return rc;
+    return D <= 64 ? launch_fwd_wg2c<64>(tq, tk, tv, tk64, tv64, p, B, s) : launch_fwd_wg2c<128>(tq, tk, tv, tk64, tv64, p, B, s);
+  }
+  if (wg2_mode() == 1 || wg2_mode() == 3)  // opt-in variant with two softmax warpgroups per CTA
     return D <= 64 ? launch_fwd_wg2<64>(tq, tk, tv, p, B, s) : launch_fwd_wg2<128>(tq, tk, tv, p, B, s);
   if (wg2_mode() == 2)  // ... and O kept in tensor memory with lazy rescaling
     return D <= 64 ? launch_fwd_wg2o<64>(tq, tk, tv, p, B, s) : launch_fwd_wg2o<128>(tq, tk, tv, p, B, s);

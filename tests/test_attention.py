@@ -83,7 +83,8 @@ def test_flash_sm100_shapes_bf16(N, D, is_causal):
 @pytest.mark.gpu
 @pytest.mark.skipif(__import__("os").environ.get("B200SYS_TEST_EXPERIMENTAL") != "1",
                     reason="opt-in kernel variants, validated on a few shapes only (set B200SYS_TEST_EXPERIMENTAL=1)")
-@pytest.mark.parametrize("env", [{"B200SYS_FA_FWD_WG2": "1"}, {"B200SYS_FA_FWD_WG2": "2"}, {"B200SYS_FA_BWD_WG": "2"},
+@pytest.mark.parametrize("env", [{"B200SYS_FA_FWD_WG2": "1"}, {"B200SYS_FA_FWD_WG2": "2"}, {"B200SYS_FA_FWD_WG2": "3"},
+                                 {"B200SYS_FA_BWD_WG": "2"},
                                  {"B200SYS_FA_BWD_WG": "4"}, {"B200SYS_FA_BWD_WG": "2r"}, {"B200SYS_FA_BWD_WG": "4r"},
                                  {"B200SYS_FA_FWD_WG2": "1", "B200SYS_FA_BWD_WG": "2"}])
 def test_flash_kernel_variants_match_oracle(env):
