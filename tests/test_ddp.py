@@ -47,3 +47,41 @@ def test_bucket_counts_match_reference_algorithm(size, expected):
     for mb in (1, 100):
         idx = sorted(i for b in plan_buckets(order, mb) for i in b)
         assert idx == list(range(len(order)))
+
+
+def test_bucket_slot_layout_invariants():
+    """Single process (no process group): every trainable parameter gets exactly one slot, slots are 32-byte aligned,
+    do not overlap, follow forward parameter order inside a bucket (so q/k/v gradients are adjacent and one wgrad
+    GEMM can produce all three)."""
+    import torch
+    from cs336_a2_systems_b200.models import TransformerLM
+    from cs336_a2_systems_b200.parallel import DDPBucketed
+
+    torch.manual_seed(0)
+    m = TransformerLM(vocab_size=50, context_length=16, d_model=32, num_layers=2, num_heads=2, d_ff=64)
+    ddp = DDPBucketed(m, bucket_size_mb=0.02)
+    assert len(ddp.buckets) > 2
+    seen = set()
+    order = {id(p): i for i, p in enumerate(m.parameters())}
+    for b in ddp.buckets:
+        idx = [order[id(p)] for p in b.params]
+        assert idx == sorted(idx), "slots inside a bucket follow forward parameter order"
+        end = 0
+        for p, off in zip(b.params, b.offsets):
+            assert id(p) not in seen
+            seen.add(id(p))
+            assert off >= end and (off * p.element_size()) % DDPBucketed.ALIGN_BYTES == 0
+            end = off + p.numel()
+        assert end <= b.numel == b.flat.numel()
+    assert seen == {id(p) for p in m.parameters() if p.requires_grad}
+    blk = m.layers[0].attn
+    where = {id(p): (bi, off) for bi, b in enumerate(ddp.buckets) for p, off in zip(b.params, b.offsets)}
+    (bq, oq), (bk, ok_), (bv, ov) = (where[id(w.weight)] for w in (blk.q_proj, blk.k_proj, blk.v_proj))
+    if bq == bk == bv:
+        assert ok_ == oq + blk.q_proj.weight.numel() and ov == ok_ + blk.k_proj.weight.numel()
+    # with a single process there is nothing to reduce: the wrapper must still train like the bare module
+    x = torch.randint(0, 50, (2, 16))
+    ddp.on_train_batch_start()
+    ddp(x).sum().backward()
+    ddp.finish_gradient_synchronization()
+    assert all(p.grad is not None for p in m.parameters())
