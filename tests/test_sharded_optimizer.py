@@ -37,3 +37,29 @@ def test_zero_bucket_slice_arithmetic():
         back = split_bucket_state(torch.cat(slices), shapes, offsets)       # what all_gather + split returns
         for a, b in zip(state, back):
             torch.testing.assert_close(a, b, rtol=0, atol=0)
+
+
+def test_partition_is_greedy_least_loaded_and_total(monkeypatch):
+    """Ownership follows the reference's rule (``ddp_bucketed_overlapped_sharded.py:342-347``: next parameter to the
+    rank with the fewest bytes so far, ties to the lowest rank), every parameter has exactly one owner, every rank
+    computes the same map, and the byte loads end up balanced for the LM's parameter mix."""
+    import torch
+    from cs336_a2_systems_b200.models import build_lm
+    from cs336_a2_systems_b200.parallel import sharded_optimizer as so
+
+    model = build_lm("small", vocab_size=1000, context_length=64, device="meta")
+    params = list(model.parameters())
+    ws = 4
+    maps = []
+    for rank in range(ws):
+        monkeypatch.setattr(so, "world", lambda r=rank: (r, ws))
+        opt = so.ShardedOptimizer(params, torch.optim.SGD, lr=0.1)
+        maps.append([opt.owner_of(p) for p in params])
+        local = [] if opt.optimizer is None else [p for g in opt.optimizer.param_groups for p in g["params"]]
+        assert {id(p) for p in local} == {id(p) for p, o in zip(params, maps[-1]) if o == rank}
+    assert all(m == maps[0] for m in maps)
+    load = [0] * ws
+    for p, o in zip(params, maps[0]):
+        assert o == min(range(ws), key=lambda r: (load[r], r))
+        load[o] += p.numel() * p.element_size()
+    assert max(load) / min(load) < 1.2
