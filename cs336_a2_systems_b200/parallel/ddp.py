@@ -29,6 +29,8 @@ tied weights are hooked once.
 
 from __future__ import annotations
 
+import os
+
 from collections import OrderedDict
 
 import torch
@@ -192,12 +194,19 @@ class DDPBucketed(_DDPBase):
         order = list(reversed(self._trainable))  # gradients become ready roughly in reverse order
         self.buckets: list[_Bucket] = []
         self._where: dict[int, tuple[int, int]] = {}
+        # in-bucket slot order: forward parameter order; opt-in (B200SYS_FUSE_W13_WGRAD=1, not yet timed on hardware)
+        # the fusion-friendly order that also puts w3 next to w1, so the SwiGLU pair gets ONE wgrad GEMM and — under
+        # the bucket-fused optimizer — an arena-resident bf16 shadow instead of a per-step re-cast
+        if os.environ.get("B200SYS_FUSE_W13_WGRAD", "0") == "1":
+            slot_pos = {id(p): k for k, p in enumerate(grad_slots.fusion_friendly_order(module))}
+        else:
+            slot_pos = {id(p): k for k, p in enumerate(module.parameters())}
         for idxs in plan_buckets(order, bucket_size_mb):
             b = _Bucket(order[idxs[0]].dtype, order[idxs[0]].device)
             align = max(1, self.ALIGN_BYTES // order[idxs[0]].element_size())
             # membership follows the (reversed) readiness order, but inside a bucket the slots are laid out in
             # forward parameter order so that q/k/v gradients are adjacent (one wgrad GEMM writes all three)
-            for i in sorted(idxs, reverse=True):
+            for i in sorted(idxs, key=lambda i: slot_pos[id(order[i])]):
                 p = order[i]
                 b.params.append(p)
                 b.offsets.append(b.numel)
