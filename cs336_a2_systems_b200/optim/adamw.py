@@ -149,6 +149,16 @@ class AdamW(torch.optim.Optimizer):
         for p in ps:  # host mirror of the device step counter (exact outside CUDA-graph replay)
             self.state[p]["t"] += 1
 
+    def refresh_device_hyper(self) -> None:
+        """Push the current ``lr`` / ``betas`` / ``eps`` / ``weight_decay`` of every param group to the device copies the
+        fused kernels read.  ``step()`` does this itself; a CUDA-graph replay does not run ``step()``, so the trainer
+        calls this before each replay — that is what keeps LR schedules working under ``cuda_graph=True``.  Copies
+        happen only when a value changed."""
+        for k, plan in self._plans.items():
+            g = self.param_groups[k if isinstance(k, int) else k[0]]
+            b1, b2 = g["betas"]
+            plan.set_hyper(g["lr"], b1, b2, g["eps"], g["weight_decay"])
+
     def sync_step_from_device(self) -> None:
         """After CUDA-graph replays the host ``t`` mirrors are stale; refresh them from the device."""
         for _key, plan in self._plans.items():

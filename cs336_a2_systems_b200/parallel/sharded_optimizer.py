@@ -82,6 +82,14 @@ class ShardedOptimizer(torch.optim.Optimizer):
         self._distribute()
         return loss
 
+    def refresh_device_hyper(self) -> None:
+        """Before a CUDA-graph replay: hand the current hyper-parameters to whatever fused path is active."""
+        if self._symm is not None and hasattr(self._symm, "refresh_device_hyper"):
+            self._symm.refresh_device_hyper()
+        elif self.optimizer is not None and hasattr(self.optimizer, "refresh_device_hyper"):
+            self._sync_hyperparameters()
+            self.optimizer.refresh_device_hyper()
+
     def _sync_hyperparameters(self) -> None:
         """LR schedules mutate ``self.param_groups``; mirror scalar hyper-parameters into the inner groups."""
         inner_by_first: dict[int, dict] = {}

@@ -138,6 +138,10 @@ class BucketFusedAdamW:
             row[:6] = torch.tensor(vals)
             self.hyper.copy_(row, non_blocking=True)
 
+    def refresh_device_hyper(self) -> None:
+        """See ``AdamW.refresh_device_hyper``: called by the trainer before a CUDA-graph replay."""
+        self._set_hyper()
+
     def _reduce_bucket(self, bi: int):
         """Called by DDPBucketed in place of its all-reduce when bucket ``bi`` is complete."""
         red = self.ddp._reducer

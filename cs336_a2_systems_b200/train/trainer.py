@@ -198,6 +198,9 @@ class Trainer:
             # the capture itself does not execute; fall through to a replay for this step
         self._static_x.copy_(x, non_blocking=True)
         self._static_y.copy_(y, non_blocking=True)
+        refresh = getattr(self.optimizer, "refresh_device_hyper", None)
+        if refresh is not None:  # LR schedules: the replay reads lr / betas / ... from device memory
+            refresh()
         self._graph.replay()
         kernels_mod.bump_param_epoch()  # the replayed optimizer kernels rewrote the parameters
         return self._static_loss
