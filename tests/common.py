@@ -1,93 +1,103 @@
-"""Shared helpers for the distributed tests: toy models, process-group setup, equivalence checks.
+"""Shared pieces of the multi-process tests: deterministic data, two toy networks, rendezvous helpers and the
+cross-rank equality check.
 
-Same protocol as the reference's ``tests/common.py:13-94`` (2-process gloo runs checked against a
-single-process model trained on the full batch); data is generated from a fixed seed instead of
-being loaded from fixture files.
+The protocol is the reference's (``tests/common.py:13-94``): two gloo processes train replicas that are compared
+with one in-process model that sees the whole batch.  What the toy networks must exercise is spelled out in
+``TOY_SPECS`` below; the regression data comes from a seeded generator rather than fixture files.
 """
 from __future__ import annotations
 
 import os
+from collections import OrderedDict
 
 import torch
 import torch.distributed as dist
-import torch.nn as nn
+from torch import nn
+
+_N_FEATURES, _N_TARGETS = 10, 5
 
 
-def make_data(n: int = 20, d_in: int = 10, d_out: int = 5):
-    g = torch.Generator().manual_seed(1234)
-    return torch.randn(n, d_in, generator=g), torch.randn(n, d_out, generator=g)
+def make_data(n: int = 20, d_in: int = _N_FEATURES, d_out: int = _N_TARGETS):
+    """``n`` regression samples ``(x[n, d_in], y[n, d_out])``, identical in every process."""
+    gen = torch.Generator().manual_seed(1234)
+    x = torch.randn(n, d_in, generator=gen)
+    y = torch.randn(n, d_out, generator=gen)
+    return x, y
 
 
-def assert_replicas_equal(net: nn.Module):
-    """Every tensor of the wrapped module's state dict must be identical on all ranks."""
-    for t in net.module.state_dict().values():
-        gathered = [torch.zeros_like(t) for _ in range(dist.get_world_size())]
-        dist.all_gather(gathered, t)
-        for other in gathered:
-            assert torch.allclose(other, t)
+class _Chain(nn.Module):
+    """ReLU MLP assembled from ``(name, d_in, d_out, bias)`` rows; the last layer has no activation."""
 
-
-class _FrozenBiasFC(nn.Module):
-    def __init__(self):
+    def __init__(self, rows):
         super().__init__()
-        self.fc = nn.Linear(10, 50, bias=True)
-        self.fc.bias.requires_grad = False
+        self._order = []
+        for name, d_in, d_out, bias in rows:
+            self.add_module(name, nn.Linear(d_in, d_out, bias=bias))
+            self._order.append(name)
 
     def forward(self, x):
-        return self.fc(x)
+        last = len(self._order) - 1
+        for i, name in enumerate(self._order):
+            x = getattr(self, name)(x)
+            if i != last:
+                x = torch.relu(x)
+        return x
 
 
-class ToyModel(nn.Module):
-    """Has a frozen bias and a frozen top-level parameter (requires_grad=False handling)."""
-
-    def __init__(self):
-        super().__init__()
-        self.fc1 = nn.Linear(10, 10, bias=False)
-        self.fc2 = _FrozenBiasFC()
-        self.fc3 = nn.Linear(50, 5, bias=False)
-        self.relu = nn.ReLU()
-        self.no_grad_fixed_param = nn.Parameter(torch.tensor([2.0, 2.0]), requires_grad=False)
-
-    def forward(self, x):
-        return self.fc3(self.relu(self.fc2(self.relu(self.fc1(x)))))
-
-
-class ToyModelWithTiedWeights(nn.Module):
-    """fc4 shares fc2's weight: the gradient hook must fire once per *parameter*."""
+class ToyModel(_Chain):
+    """10 → 10 → 50 → 5.  The middle layer carries a bias that is frozen, and the model owns a frozen top-level
+    parameter: DDP wrappers must skip ``requires_grad=False`` tensors when hooking and bucket accounting, yet still
+    broadcast them."""
 
     def __init__(self):
-        super().__init__()
-        self.fc1 = nn.Linear(10, 10, bias=False)
-        self.fc2 = nn.Linear(10, 50, bias=False)
-        self.fc3 = nn.Linear(50, 10, bias=False)
-        self.fc4 = nn.Linear(10, 50, bias=False)
-        self.fc5 = nn.Linear(50, 5, bias=False)
+        super().__init__([("fc1", _N_FEATURES, 10, False), ("fc2", 10, 50, True), ("fc3", 50, _N_TARGETS, False)])
+        self.fc2.bias.requires_grad_(False)
+        self.no_grad_fixed_param = nn.Parameter(torch.full((2,), 2.0), requires_grad=False)
+
+
+class ToyModelWithTiedWeights(_Chain):
+    """10 → 10 → 50 → 10 → 50 → 5 where the 4th layer re-uses the 2nd layer's weight: one parameter, two uses — a
+    gradient hook must fire once for it, after both contributions have been accumulated."""
+
+    def __init__(self):
+        super().__init__([("fc1", _N_FEATURES, 10, False), ("fc2", 10, 50, False), ("fc3", 50, 10, False),
+                          ("fc4", 10, 50, False), ("fc5", 50, _N_TARGETS, False)])
         self.fc4.weight = self.fc2.weight
-        self.relu = nn.ReLU()
 
-    def forward(self, x):
-        x = self.relu(self.fc1(x))
-        x = self.relu(self.fc2(x))
-        x = self.relu(self.fc3(x))
-        x = self.relu(self.fc4(x))
-        return self.fc5(x)
+
+TOY_SPECS = OrderedDict(
+    frozen=("ToyModel", "frozen bias inside a layer + frozen top-level parameter"),
+    tied=("ToyModelWithTiedWeights", "one weight shared by two layers"),
+)
+
+
+def assert_replicas_equal(net: nn.Module) -> None:
+    """Collective: every entry of the wrapped module's state dict is the same on all ranks."""
+    world = dist.get_world_size()
+    for key, mine in net.module.state_dict().items():
+        copies = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(copies, mine)
+        for r, theirs in enumerate(copies):
+            assert torch.allclose(theirs, mine), f"{key} differs between this rank and rank {r}"
 
 
 def setup_process_group(rank: int, world_size: int, backend: str, port: int) -> str:
-    os.environ["MASTER_ADDR"] = "127.0.0.1"
-    os.environ["MASTER_PORT"] = str(port)
-    if torch.cuda.is_available() and torch.cuda.device_count() > 0:
-        # like the reference's helper: tensors go to cuda:(rank % n) even under gloo, so on a 1-GPU
-        # box both ranks share cuda:0 and the wrappers must fall back to torch.distributed
-        local = rank % torch.cuda.device_count()
-        torch.cuda.set_device(local)
-        device = f"cuda:{local}"
-    else:
-        device = "cpu"
+    """Rendezvous on 127.0.0.1:``port`` and return the device string this rank should use.
+
+    As in the reference's helper a CUDA box maps rank r to ``cuda:(r mod #gpus)`` whatever the backend — with one GPU
+    both gloo ranks land on ``cuda:0``, which is exactly the case where the wrappers have to fall back from the NVLink
+    kernels to plain ``torch.distributed`` collectives."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    device = "cpu"
+    n_gpu = torch.cuda.device_count() if torch.cuda.is_available() else 0
+    if n_gpu:
+        index = rank % n_gpu
+        torch.cuda.set_device(index)
+        device = f"cuda:{index}"
     dist.init_process_group(backend, rank=rank, world_size=world_size)
     return device
 
 
-def cleanup_process_group():
+def cleanup_process_group() -> None:
     dist.barrier()
     dist.destroy_process_group()
