@@ -44,3 +44,19 @@ def test_model_flags_broken_protocols():
     assert _caught(lambda s: ps.sim_bwd_reordered(5, seed=s, mutate="no_dq_full_wait")) > 0
     assert _caught(lambda s: ps.sim_bwd_reordered(5, seed=s, mutate="no_dq_empty_wait")) > 0
     assert _caught(lambda s: ps.sim_fwd_cluster((6, 6), seed=s, mutate="local_release")) > 0
+
+
+def test_cross_rank_flag_barrier_protocol():
+    """The 1-deep flag channels of the NVLink kernels' cross-rank barrier: back-to-back kernels re-use the same words
+    without losing or duplicating an arrival, also when only part of a grid is resident (in-order block dispatch)."""
+    for seed in range(4):
+        ps.sim_cross_rank_barrier(ws=4, blocks=5, kernels=4, seed=seed)
+        ps.sim_cross_rank_barrier(ws=3, blocks=6, kernels=3, resident=2, seed=seed)
+
+
+def test_model_reproduces_the_partial_residency_hazard():
+    """Known limit of per-block cross-rank barriers: a grid that is not fully co-resident deadlocks if the ranks'
+    block schedulers dispatch blocks in different orders.  (The kernels rely on in-order dispatch and on grids of at
+    most one CTA per SM.)"""
+    with pytest.raises(AssertionError):
+        ps.sim_cross_rank_barrier(ws=3, blocks=8, kernels=1, resident=3, seed=1, shuffled_launch=True)

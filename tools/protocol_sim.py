@@ -476,6 +476,65 @@ def sim_fwd_o_in_tmem(n_kv, n_warps=8, seed=0, p_correct=0.5, mutate=None):
     return S.now
 
 
+# ------------------------------------------------------------------------------------------------
+# Cross-rank flag barrier of the NVLink kernels (csrc/comm_adamw.cu: zbarrier; comm_allreduce.cu: cross_rank_barrier)
+# ------------------------------------------------------------------------------------------------
+def sim_cross_rank_barrier(ws=4, blocks=6, kernels=5, resident=None, seed=0, shuffled_launch=False):
+    """Every rank runs the same sequence of kernels; block b of rank r synchronises with block b of every other rank at
+    the start and at the end of each kernel through 1-deep flag channels (sender CAS 0→1 on the peer's word, receiver
+    CAS 1→0 on its own).  ``resident`` bounds how many blocks of a rank can be on the GPU at once; with
+    ``shuffled_launch`` the block scheduler of each rank picks the next block in its own random order — the case in
+    which a grid that is not fully co-resident can deadlock."""
+    S = Sim(seed)
+    flag = {}  # (dst_rank, block, src_rank) -> 0/1
+
+    class Chan:
+        def __init__(self, key):
+            self.key, self.name = key, f"flag{key}"
+
+    def send(dst, b, src):
+        while flag.get((dst, b, src), 0) != 0:
+            yield ("delay", 1)
+        flag[(dst, b, src)] = 1
+
+    def recv(me, b, src):
+        while flag.get((me, b, src), 0) != 1:
+            yield ("delay", 1)
+        flag[(me, b, src)] = 0
+
+    slots = {r: (resident or blocks) for r in range(ws)}
+    done_blocks = {(r, k): 0 for r in range(ws) for k in range(kernels)}
+    reads = {}
+
+    def block(r, k, b):
+        # kernel k starts on rank r only after kernel k-1 finished there (same stream)
+        while k > 0 and done_blocks[(r, k - 1)] < blocks:
+            yield ("delay", 1)
+        while slots[r] == 0:
+            yield ("delay", 1)
+        slots[r] -= 1
+        for phase in range(2):
+            for peer in range(ws):
+                yield from send(peer, b, r)
+            for peer in range(ws):
+                yield from recv(r, b, peer)
+            if phase == 0:
+                reads[(r, k, b)] = S.now       # after the first barrier every rank has entered kernel k
+                yield ("delay", S.jitter(1, 20))
+        slots[r] += 1
+        done_blocks[(r, k)] += 1
+
+    for r in range(ws):
+        for k in range(kernels):
+            order = list(range(blocks))
+            if shuffled_launch:
+                S.rng.shuffle(order)
+            for b in order:
+                S.spawn(f"r{r}k{k}b{b}", block(r, k, b))
+    S.run(limit=200_000)
+    return S.now
+
+
 def main():
     for n in range(0, 7):
         for seed in range(20):
@@ -489,6 +548,10 @@ def main():
         for seed in range(20):
             sim_fwd_o_in_tmem(n, seed=seed)
     print("forward, O in tensor memory with lazy rescale: ok")
+    for seed in range(10):
+        sim_cross_rank_barrier(ws=4, blocks=6, kernels=4, seed=seed)
+        sim_cross_rank_barrier(ws=3, blocks=8, kernels=3, resident=3, seed=seed)  # in-order launch: partial residency is fine
+    print("cross-rank flag barrier: ok")
 
 
 if __name__ == "__main__":
