@@ -91,6 +91,44 @@ def test_flash_pytorch_random_shapes():
     check()
 
 
+def test_lazy_rescale_recurrence_is_exact():
+    """The recurrence of the O-in-tensor-memory forward variant (``fa2_fwd_wg2o_kernel``), restated in PyTorch: the
+    exponentials are taken against a reference maximum that only moves when the true maximum exceeds it by 2^tau, O and
+    l are rescaled only then, and L = m_ref·ln2 + ln(l).  Whatever the reference, O / l and L must equal the exact
+    softmax attention; P never exceeds 2^tau."""
+    import math
+
+    torch.manual_seed(3)
+    B, N, D, T, tau = 2, 96, 16, 16, 8.0
+    q, k, v = torch.randn(B, N, D) * 3, torch.randn(B, N, D) * 3, torch.randn(B, N, D)
+    scale_log2 = (1.0 / math.sqrt(D)) * math.log2(math.e)
+    o_ref, l_ref = attention_and_lse_ref(q, k, v, True)
+    m_ref = torch.full((B, N), -float("inf"))
+    l = torch.zeros(B, N)
+    o = torch.zeros(B, N, D)
+    p_max, n_moves = 0.0, 0
+    rows = torch.arange(N)[:, None]
+    for j in range(N // T):
+        s = torch.einsum("bqd,bkd->bqk", q, k[:, j * T:(j + 1) * T]) * scale_log2
+        mask = rows >= (torch.arange(T)[None, :] + j * T)
+        s = torch.where(mask, s, torch.full_like(s, -float("inf")))
+        m_tile = s.amax(-1)
+        move = m_tile > m_ref + tau
+        m_new = torch.where(move, m_tile, m_ref)
+        m_use = torch.where(torch.isinf(m_new), torch.zeros_like(m_new), m_new)
+        alpha = torch.where(move, torch.exp2(m_ref - m_use), torch.ones_like(m_ref))
+        p = torch.where(mask, torch.exp2(s - m_use[..., None]), torch.zeros_like(s))
+        p_max = max(p_max, float(p.max()))
+        n_moves += int(move.sum())
+        o = o * alpha[..., None] + torch.einsum("bqk,bkd->bqd", p, v[:, j * T:(j + 1) * T])
+        l = l * alpha + p.sum(-1)
+        m_ref = m_new
+    torch.testing.assert_close(o / l[..., None], o_ref, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close((m_ref + torch.log2(l)) * math.log(2.0), l_ref, rtol=1e-5, atol=1e-5)
+    assert p_max <= 2.0 ** tau * (1 + 1e-6)
+    assert n_moves < B * N * (N // T) // 2  # the rescale is the exception, not the rule
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("is_causal", [False, True])
 def test_flash_forward_pass_sm100(is_causal):
