@@ -131,11 +131,25 @@ def build_ours(args, rank, ws, dev):
     if shard and ws > 1 and not getattr(getattr(model, "_reducer", None), "kind", "") == "symm":
         shard = args.sharded  # the fused path needs the NVLink backend; an explicit --sharded still gets the generic one
     args.shard_effective = bool(shard and ws > 1)
+    opt = None
     if shard and ws > 1:
         from cs336_a2_systems_b200.parallel import ShardedOptimizer
-        opt = ShardedOptimizer(model.parameters(), AdamW, **kw)
-        fused_sharded = opt.enable_symmetric(model)
-    else:
+        explicit = args.sharded or args.optimizer == "sharded"
+        try:
+            opt = ShardedOptimizer(model.parameters(), AdamW, **kw)
+            fused_sharded = opt.enable_symmetric(model)
+        except Exception as e:  # e.g. the symmetric parameter arenas cannot be mapped on this box
+            if explicit:
+                raise
+            print(f"[bench] fused sharded optimizer unavailable ({type(e).__name__}: {e}); using replicated AdamW",
+                  file=sys.stderr)
+            opt = None
+        if opt is not None and not explicit and not hasattr(getattr(opt, "_symm", None), "_reduce_bucket"):
+            opt = None  # 'auto' only wants the bucket-fused path; anything else is slower than replicated AdamW
+        if opt is None:
+            fused_sharded = False
+            args.shard_effective = False
+    if opt is None:
         opt = AdamW(model.parameters(), **kw)
     bucket_fused = hasattr(getattr(opt, "_symm", None), "_reduce_bucket")
     trainer = Trainer(model, opt, autocast=True,
