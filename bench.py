@@ -48,8 +48,14 @@ def parse_args():
     ap.add_argument("--optimizer", choices=["auto", "replicated", "sharded"], default="auto",
                     help="ours, N>1: 'sharded' = AdamW state sharded 1/N per rank with the update fused into the "
                          "per-bucket NVLink reduce kernel (every rank still ends the step with all updated fp32 "
-                         "parameters); 'replicated' = all-reduce then full AdamW on every rank; 'auto' = sharded for "
-                         "2..4 ranks (measured faster), replicated otherwise")
+                         "parameters); 'replicated' = all-reduce then full AdamW on every rank; 'auto' = sharded "
+                         "whenever the NVLink backend is available (all ranks agree on the outcome)")
+    ap.add_argument("--defer-gather", choices=["auto", "0", "1"], default="auto",
+                    help="ours, sharded: refresh the fp32 replicas of Linear weights under the NEXT forward instead "
+                         "of inside the backward-overlapped bucket kernels (bf16 GEMM shadows and fp32-read "
+                         "parameters are always distributed at once); 'auto' = on from 4 ranks up")
+    ap.add_argument("--zero-variant", type=int, default=None,
+                    help="ours, sharded: bucket kernel variant (bit 0 NVLS reduce, bit 1 NVLS stores); default by N")
     ap.add_argument("--watchdog-s", type=float, default=420.0,
                     help="abort the whole process (exit code 3, one JSON error line) if the run has not finished "
                          "after this many seconds, instead of sitting in a collective until its 10-minute timeout")
@@ -127,35 +133,41 @@ def build_ours(args, rank, ws, dev):
         model = DDPBucketed(model, bucket_size_mb=args.bucket_mb, backend=args.comm)
     kw = dict(lr=1e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
     fused_sharded = False
-    shard = args.sharded or args.optimizer == "sharded" or (args.optimizer == "auto" and 2 <= ws <= 4)
-    if shard and ws > 1 and not getattr(getattr(model, "_reducer", None), "kind", "") == "symm":
-        shard = args.sharded  # the fused path needs the NVLink backend; an explicit --sharded still gets the generic one
-    args.shard_effective = bool(shard and ws > 1)
+    symm_backend = getattr(getattr(model, "_reducer", None), "kind", "") == "symm"
+    explicit = args.sharded or args.optimizer == "sharded"
+    shard = ws > 1 and (explicit or (args.optimizer == "auto" and symm_backend))
+    defer = (ws >= 4) if args.defer_gather == "auto" else args.defer_gather == "1"
     opt = None
-    if shard and ws > 1:
+    if shard:
         from cs336_a2_systems_b200.parallel import ShardedOptimizer
-        explicit = args.sharded or args.optimizer == "sharded"
+        err = None
         try:
             opt = ShardedOptimizer(model.parameters(), AdamW, **kw)
-            fused_sharded = opt.enable_symmetric(model)
+            fused_sharded = opt.enable_symmetric(model, defer_fp32_gather=defer, variant=args.zero_variant)
         except Exception as e:  # e.g. the symmetric parameter arenas cannot be mapped on this box
+            err = e
+        # every rank must take the same path (the fused kernels meet at cross-rank barriers): agree on the outcome
+        ok = torch.tensor([0 if err is not None else 1], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 0:
             if explicit:
-                raise
-            print(f"[bench] fused sharded optimizer unavailable ({type(e).__name__}: {e}); using replicated AdamW",
-                  file=sys.stderr)
+                raise err if err is not None else RuntimeError("sharded optimizer setup failed on another rank")
+            print(f"[bench] fused sharded optimizer unavailable ({type(err).__name__ if err else 'peer'}: {err}); "
+                  "using replicated AdamW", file=sys.stderr)
             opt = None
         if opt is not None and not explicit and not hasattr(getattr(opt, "_symm", None), "_reduce_bucket"):
             opt = None  # 'auto' only wants the bucket-fused path; anything else is slower than replicated AdamW
         if opt is None:
             fused_sharded = False
-            args.shard_effective = False
+    args.shard_effective = opt is not None
     if opt is None:
         opt = AdamW(model.parameters(), **kw)
     bucket_fused = hasattr(getattr(opt, "_symm", None), "_reduce_bucket")
     trainer = Trainer(model, opt, autocast=True,
                       cuda_graph=not args.no_graph and (bucket_fused or not args.shard_effective),
-                      overlap_optimizer=not args.no_overlap and not args.shard_effective)
-    state = {"launches_per_step": 0}
+                      overlap_optimizer=not args.no_overlap and not args.shard_effective,
+                      graph_warmup_steps=2)
+    state = {"launches_per_step": 0, "trainer": trainer, "optimizer": opt}
 
     def step_device(x, y):
         return trainer.step(x, y)
@@ -163,16 +175,19 @@ def build_ours(args, rank, ws, dev):
     def step_e2e(xh, yh):
         return trainer.step_from_host(xh, yh)
 
-    def count_launches(x, y):
-        n0 = kernels.native_launches()  # counted inside libb200sys.so at every launch site
-        trainer._step_eager(x, y)
-        state["launches_per_step"] = kernels.native_launches() - n0
+    def launches_now():
+        """Kernels of libb200sys.so launched so far: counted at every launch site inside the library; a CUDA-graph
+        replay launches exactly the kernels counted while the step was captured."""
+        return kernels.native_launches() + trainer.graph_replays * trainer.graph_kernel_count
 
+    sym = getattr(opt, "_symm", None)
     extra = {"cuda_graph": trainer.cuda_graph, "optimizer_overlapped_with_backward": trainer._overlap is not None,
              "sharded_optimizer": args.shard_effective, "fused_nvlink_sharded_adamw": fused_sharded,
              "bucket_fused_reduce_scatter_adamw_allgather": bucket_fused,
+             "zero_kernel_variant": getattr(sym, "variant", None) if bucket_fused else None,
+             "deferred_fp32_param_gather": bool(getattr(sym, "defer", False)) if bucket_fused else None,
              "comm": getattr(getattr(model, "_reducer", None), "kind", "none")}
-    return step_device, step_e2e, count_launches, state, extra
+    return step_device, step_e2e, launches_now, state, extra
 
 
 # ------------------------------------------------------------------------------------------------
@@ -261,23 +276,23 @@ def _main(args):
     from cs336_a2_systems_b200.utils.clocks import ClockSampler
 
     build = build_ours if args.impl == "ours" else build_reference
-    step_device, step_e2e, count_launches, state, extra = build(args, rank, ws, dev)
+    step_device, step_e2e, launches_now, state, extra = build(args, rank, ws, dev)
 
     n_pool = 8
     xs_h, ys_h = make_batches(n_pool, args.batch, args.ctx, args.vocab, seed=99 + rank)
     xs_d = [x.to(dev) for x in xs_h]
     ys_d = [y.to(dev) for y in ys_h]
 
-    # ---- warm-up (also builds optimizer plans / weight shadows / captures the CUDA graph)
-    if count_launches is not None:
-        count_launches(xs_d[0], ys_d[0])
-    n_warm = max(args.warmup, 3) + (4 if args.impl == "ours" and not args.no_graph else 0)
-    loss0 = None
+    # ---- warm-up: the same W steps for both arms (ours builds optimizer plans and weight shadows in the first two
+    #      and captures the CUDA graph in the third, so W >= 3 leaves only replays in the timed region)
+    n_warm = max(args.warmup, 3)
+    loss_at = {}
     for i in range(n_warm):
         loss = step_device(xs_d[i % n_pool], ys_d[i % n_pool])
         if i == 0:
-            loss0 = float(loss.item())
+            loss_at[1] = float(loss.item())
     torch.cuda.synchronize()
+    n_launch0 = launches_now() if launches_now is not None else 0
 
     # ---- timed: device-resident inputs
     local = dev.index or 0
@@ -293,18 +308,41 @@ def _main(args):
 
         ms_e2e = timed_loop(e2e, args.steps, ws, dev)
     clocks = clk.summary()
+    n_launched = (launches_now() - n_launch0) if launches_now is not None else None
+    comm_dead = None
+    if args.impl == "ours":
+        from cs336_a2_systems_b200.ops import kernels as _k
+        if hasattr(state.get("optimizer"), "sync_params"):
+            state["optimizer"].sync_params()  # the last step's deferred fp32 gather
+            torch.cuda.synchronize()
+        comm_dead = _k.comm_status()
 
     tokens_per_step = ws * args.batch * args.ctx
     ms_per_step = ms_dev / args.steps
     value = tokens_per_step / (ms_per_step / 1e3)
     e2e_value = tokens_per_step / (ms_e2e / args.steps / 1e3)
     final_loss = last.get("loss")
+    loss_at[n_warm + 2 * args.steps] = final_loss
+    peak = torch.cuda.max_memory_allocated() / 2 ** 30
+    peaks = [peak]
+    if ws > 1:
+        t = torch.tensor([peak], dtype=torch.float64, device=dev)
+        allp = [torch.zeros_like(t) for _ in range(ws)]
+        dist.all_gather(allp, t)
+        peaks = [float(a.item()) for a in allp]
     if rank == 0:
         from cs336_a2_systems_b200.models import get_model_config
         cfg = get_model_config(args.model)
+        if args.impl == "reference":
+            placement = "reference ShardedStateOptimizer(AdamW)" if extra.get("sharded_optimizer") else "reference AdamW, replicated"
+        elif extra.get("bucket_fused_reduce_scatter_adamw_allgather"):
+            placement = "AdamW state sharded 1/N (ZeRO-1), update fused into the per-bucket NVLink reduce kernel"
+        elif extra.get("sharded_optimizer"):
+            placement = "AdamW state sharded by parameter owner"
+        else:
+            placement = "AdamW replicated"
         out = {
-            "metric": "XL LM train tokens/s (bucketed DDP, bf16 autocast, AdamW)" if args.model == "xl" and not args.sharded
-                      else f"{args.model} LM train tokens/s" + (" (DDP + sharded optimizer)" if args.sharded else ""),
+            "metric": f"{args.model.upper()} LM train tokens/s (bucketed DDP, bf16 autocast, {placement})",
             "value": round(value, 1), "unit": "tokens/s", "n_gpus": ws, "steps": args.steps, "warmup": n_warm,
             "ms_per_step": round(ms_per_step, 3), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic tokens, random-init weights",
@@ -312,22 +350,23 @@ def _main(args):
             "config": {"model": args.model, **cfg, "vocab": args.vocab, "seq_len": args.ctx,
                        "global_batch": ws * args.batch, "per_gpu_batch": args.batch,
                        "parallelism": f"dp{ws}", "bucket_size_mb": args.bucket_mb,
-                       "optimizer": ("AdamW fp32 state, sharded 1/N per rank (ZeRO-1), update fused into the "
-                                     "per-bucket NVLink reduce-scatter/all-gather kernel")
-                       if extra.get("bucket_fused_reduce_scatter_adamw_allgather") else
-                       ("AdamW fp32 state, sharded by parameter owner" if extra.get("sharded_optimizer")
-                        else "AdamW fp32 state, replicated"),
+                       "optimizer": placement,
                        "l2": "no flush: ~30 GB working set per step >> 126 MB L2", **extra},
             "e2e": {"value": round(e2e_value, 1), "unit": "tokens/s", "ms_per_step": round(ms_e2e / args.steps, 3),
                     "h2d_bytes_per_step": 2 * args.batch * args.ctx * 8, "d2h_bytes_per_step": 4},
-            "gpu_launches": (state["launches_per_step"] or 0) * args.steps * 2 if args.impl == "ours" else None,
-            "launches_per_step": state["launches_per_step"],
+            # kernels of libb200sys.so launched inside the two timed loops (2 x steps steps): library-side counter,
+            # graph replays counted as the kernels recorded at capture
+            "gpu_launches": n_launched,
+            "launches_per_step": (n_launched // (2 * args.steps)) if n_launched else None,
             "clocks": {"sm_mhz": clocks.get("sm_mhz"), "sm_max_mhz": clocks.get("sm_max_mhz"),
                        "reasons": clocks.get("reasons"), "samples": clocks.get("samples"),
                        "power_w_max": clocks.get("power_w_max")},
-            "loss_first": loss0, "loss_last": final_loss,
-            "peak_mem_gib": round(torch.cuda.max_memory_allocated() / 2 ** 30, 2),
+            "loss_at_step": {str(k): v for k, v in loss_at.items()},
+            "loss_first": loss_at.get(1), "loss_last": final_loss,
+            "peak_mem_gib": round(max(peaks), 2), "peak_mem_gib_per_rank": [round(x, 2) for x in peaks],
         }
+        if comm_dead is not None:
+            out["error"] = "NVLink communicator reported a timed-out barrier (rank, cta, peer, phase, slot, flag) = %s" % (comm_dead,)
         print(json.dumps(out), flush=True)
     if ws > 1:
         dist.barrier()

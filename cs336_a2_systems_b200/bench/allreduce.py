@@ -16,21 +16,12 @@ import torch.distributed as dist
 
 from ..ops import kernels
 from ..parallel import setup, symm
-from ..utils.timing import max_over_ranks
+from ..utils.clocks import ClockSampler
+from ..utils.timing import time_collective
 
 
 def _time(fn, warmup, iters, dev):
-    for _ in range(warmup):
-        fn()
-    torch.cuda.synchronize(dev)
-    dist.barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(iters):
-        fn()
-    e1.record()
-    torch.cuda.synchronize(dev)
-    return max_over_ranks(e0.elapsed_time(e1) / iters, dev)
+    return time_collective(fn, warmup, iters, dev)
 
 
 def main():
@@ -55,6 +46,7 @@ def main():
         buf.normal_()
         ref = buf.clone()
         res = {"size_mb": mb, "world_size": ws}
+        sampler = ClockSampler(dev.index or 0, period_ms=50).__enter__()
         t = _time(lambda: dist.all_reduce(ref), args.warmup, args.iters, dev)
         res["nccl_ms"] = t
         for name, algo in algos.items():
@@ -65,11 +57,20 @@ def main():
             res[f"{name}_ms"] = t
         # bus bandwidth (NCCL convention): 2 (ws-1)/ws * S / t
         for k in list(res):
-            if k.endswith("_ms"):
+            if k.endswith("_ms") and not k.startswith("bcast"):
                 res[k.replace("_ms", "_busbw_gbs")] = 2 * (ws - 1) / ws * n * 4 / (res[k] * 1e-3) / 1e9
+        if n * 4 >= 1 << 20:
+            # parameter broadcast from rank 0: NCCL vs pull (ws-1 readers) vs one multicast store through the switch
+            res["bcast_nccl_ms"] = _time(lambda: dist.broadcast(ref, src=0), args.warmup, args.iters, dev)
+            res["bcast_pull_ms"] = _time(lambda: kernels.bcast_pull(arena, 0, n * 4, 0), args.warmup, args.iters, dev)
+            if arena.multicast_ptr:
+                res["bcast_mc_ms"] = _time(lambda: kernels.bcast_mc(arena, 0, n * 4, 0), args.warmup, args.iters, dev)
+        sampler.__exit__()
+        res["clocks"] = sampler.summary()  # rank 0's GPU while this row ran
         rows.append(res)
         if rank == 0:
             print(json.dumps(res), flush=True)
+    kernels.comm_check()
     if rank == 0 and args.json:
         json.dump(rows, open(args.json, "w"), indent=1)
     dist.barrier()

@@ -8,6 +8,12 @@ plus the course leaderboard shape (16 heads × 16384 × 64, bf16, causal).  Impl
 * ``reference`` — the unmodified reference ``FlashAttentionTriton`` (Triton forward + its backward) from
                   ``baseline/_ref`` when installed (``--with-reference``)
 * ``eager``     — materialised PyTorch attention (the reference LM's ``scaled_dot_product_attention``)
+* ``materialized`` — the same O(N²) algorithm on this library's kernels (tcgen05 GEMMs + one fused
+                  scale/mask/softmax row kernel): the counterpart of the reference's ``torch.compile``d attention arm
+
+``--protocol batch8`` is the reference's second attention benchmark (``benchmark_attention.py:113-201``): batch 8,
+seq 256…16384 × d 16…128, forward / backward time and peak memory of the eager, materialized and flash arms.
+Every row carries the clocks sampled while it ran.
 
 CUDA-event timing after warm-up, L2 flushed between iterations; OOM is caught and recorded as null
 (the reference's backward materialises N×N matrices).  Output: JSON lines + a Markdown table.
@@ -25,6 +31,7 @@ import torch
 
 from ..ops.attention import FlashAttentionSM100
 from ..ops.functional import sdpa_ref
+from ..utils.clocks import ClockSampler
 from ..utils.timing import time_cuda
 
 
@@ -78,15 +85,23 @@ def run(shapes, dtypes, impls, iters, warmup, ref=None):
                     fn = lambda a, b, c: FlashAttentionSM100.apply(a, b, c, True)
                 elif impl == "reference":
                     fn = lambda a, b, c: ref.FlashAttentionTriton.apply(a, b, c, True)
+                elif impl == "materialized":
+                    if N > 16384:
+                        continue
+                    from ..ops import native
+                    fn = lambda a, b, c: native.materialized_attention(a, b, c, True)
                 else:
                     mask = torch.ones(N, N, device=dev, dtype=torch.bool).tril() if N <= 16384 else None
                     if mask is None:
                         continue
                     fn = lambda a, b, c: sdpa_ref(a, b, c, mask)
                 n_it = max(2, min(iters, int(2e9 / (N * N))))  # keep the eager/reference sweeps bounded
-                r = _bench_impl(fn, q, k, v, n_it, warmup)
+                torch.cuda.reset_peak_memory_stats()
+                with ClockSampler(0, period_ms=50) as clk:
+                    r = _bench_impl(fn, q, k, v, n_it, warmup)
                 ff, fb = _flops(1, BH, N, D, True)
-                row = dict(impl=impl, heads=BH, seq=N, d=D, dtype=str(dt).split(".")[-1], **r)
+                row = dict(impl=impl, heads=BH, seq=N, d=D, dtype=str(dt).split(".")[-1], **r,
+                           peak_mem_mib=round(torch.cuda.max_memory_allocated() / 2 ** 20, 1), clocks=clk.summary())
                 if r.get("fwd_ms"):
                     row["fwd_tflops"] = ff / r["fwd_ms"] / 1e9
                 if r.get("bwd_ms"):
@@ -99,11 +114,14 @@ def run(shapes, dtypes, impls, iters, warmup, ref=None):
 
 
 def markdown(rows):
-    out = ["| impl | heads | seq | d | dtype | fwd ms | bwd ms | fwd+bwd ms | fwd TF/s | bwd TF/s |", "|---|---|---|---|---|---|---|---|---|---|"]
+    out = ["| impl | heads | seq | d | dtype | fwd ms | bwd ms | fwd+bwd ms | fwd TF/s | bwd TF/s | peak MiB | SM MHz | throttle |",
+           "|---|---|---|---|---|---|---|---|---|---|---|---|---|"]
     f = lambda x: "n/a" if x is None else (f"{x:.3f}" if isinstance(x, float) else str(x))
     for r in rows:
         out.append(f"| {r['impl']} | {r['heads']} | {r['seq']} | {r['d']} | {r['dtype']} | {f(r.get('fwd_ms'))} | "
-                   f"{f(r.get('bwd_ms'))} | {f(r.get('fwdbwd_ms'))} | {f(r.get('fwd_tflops', '-'))} | {f(r.get('bwd_tflops', '-'))} |")
+                   f"{f(r.get('bwd_ms'))} | {f(r.get('fwdbwd_ms'))} | {f(r.get('fwd_tflops', '-'))} | {f(r.get('bwd_tflops', '-'))} | "
+                   f"{f(r.get('peak_mem_mib'))} | {f((r.get('clocks') or {}).get('sm_mhz'))} | "
+                   f"{','.join((r.get('clocks') or {}).get('reasons') or []) or '-'} |")
     return "\n".join(out)
 
 
@@ -112,12 +130,19 @@ def main():
     ap.add_argument("--quick", action="store_true", help="a handful of shapes instead of the full sweep")
     ap.add_argument("--with-reference", action="store_true")
     ap.add_argument("--with-eager", action="store_true")
+    ap.add_argument("--with-materialized", action="store_true")
+    ap.add_argument("--protocol", choices=["sweep", "batch8"], default="sweep")
+    ap.add_argument("--dtypes", nargs="+", default=["bfloat16", "float32"])
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--json", default=None)
     ap.add_argument("--md", default=None)
     args = ap.parse_args()
-    if args.quick:
+    if args.protocol == "batch8":
+        seqs = (256, 4096) if args.quick else (256, 1024, 4096, 8192, 16384)
+        shapes = [(8, n, d) for n in seqs for d in ((64,) if args.quick else (16, 32, 64, 128))]
+        dtypes = [getattr(torch, d) for d in args.dtypes]
+    elif args.quick:
         shapes = [(16, 16384, 64), (1, 4096, 64), (1, 16384, 128), (100, 512, 64)]
         dtypes = [torch.bfloat16, torch.float32]
     else:
@@ -135,8 +160,10 @@ def main():
             impls.append("reference")
         else:
             print(json.dumps({"reference_unavailable": why}))
-    if args.with_eager:
+    if args.with_eager or args.protocol == "batch8":
         impls.append("eager")
+    if args.with_materialized or args.protocol == "batch8":
+        impls.append("materialized")
     rows = run(shapes, dtypes, impls, args.iters, args.warmup, ref)
     if args.json:
         json.dump(rows, open(args.json, "w"), indent=1)

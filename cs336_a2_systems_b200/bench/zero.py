@@ -21,6 +21,7 @@ import torch.distributed as dist
 from .. import _native
 from ..ops import kernels
 from ..parallel import setup, symm
+from ..utils.clocks import ClockSampler
 from .allreduce import _time
 
 
@@ -57,13 +58,23 @@ def main():
         v = torch.zeros(per * 8, dtype=torch.float32, device=dev)
         res = {"size_mb": mb, "world_size": ws}
 
-        def fused(variant, shadow, blocks):
+        sampler = ClockSampler(dev.index or 0, period_ms=50).__enter__()
+        none8 = (ctypes.c_longlong * 8)()
+        table = torch.tensor([[0, nvec]], dtype=torch.int64, device=dev)
+
+        def fused(variant, shadow, blocks, defer=0):
             _native.check(lib.b200_zero_adamw_bucket(
                 garena.peer_ptrs_c, parena.peer_ptrs_c, sarena.peer_ptrs_c if shadow else None, garena.signal_ptrs_c,
                 mc, ctypes.c_longlong(0), ctypes.c_longlong(n), _native.p(m), _native.p(v),
                 _native.p(hyper), _native.p(step), ctypes.c_int(0), ctypes.c_int(rank), ctypes.c_int(ws),
-                ctypes.c_int(blocks), ctypes.c_int(0), ctypes.c_int(variant), ctypes.c_void_p(stream.cuda_stream)),
-                "zero_adamw_bucket")
+                ctypes.c_int(blocks), ctypes.c_int(0), ctypes.c_int(variant), ctypes.c_int(defer), ctypes.c_int(0),
+                none8, none8, ctypes.c_void_p(stream.cuda_stream)), "zero_adamw_bucket")
+
+        def gather(use_mc):
+            _native.check(lib.b200_zero_param_gather(
+                parena.peer_ptrs_c, garena.signal_ptrs_c, ctypes.c_ulonglong(parena.multicast_ptr if use_mc else 0),
+                _native.p(table), ctypes.c_int(1), ctypes.c_int(rank), ctypes.c_int(ws), ctypes.c_int(0),
+                ctypes.c_int(0), ctypes.c_void_p(stream.cuda_stream)), "zero_param_gather")
 
         names = {0: "p2p", 1: "nvlsld_p2pst", 2: "p2pld_nvlsst", 3: "nvls"}
         for blocks in args.blocks:
@@ -71,6 +82,12 @@ def main():
                 for shadow in (True, False):
                     key = f"fused_{names[variant]}_{'shadow' if shadow else 'noshadow'}_b{blocks}"
                     res[key + "_ms"] = _time(lambda: fused(variant, shadow, blocks), args.warmup, args.iters, dev)
+                # deferred fp32 gather: the bucket kernel moves the shadows only; the gather kernel is timed apart
+                res[f"fused_{names[variant]}_defer_b{blocks}_ms"] = _time(lambda: fused(variant, True, blocks, 1),
+                                                                         args.warmup, args.iters, dev)
+        res["param_gather_p2p_ms"] = _time(lambda: gather(False), args.warmup, args.iters, dev)
+        if mc is not None:
+            res["param_gather_nvls_ms"] = _time(lambda: gather(True), args.warmup, args.iters, dev)
         sh_all = sarena.view(0, n, torch.bfloat16)
         res["local_shadow_cast_ms"] = _time(lambda: kernels.cast_bf16(p, sh_all), args.warmup, args.iters, dev)
         # the two-step path: all-reduce (auto algorithm) + replicated AdamW over the whole bucket
@@ -86,12 +103,15 @@ def main():
         S = n * 4
         res["nvlink_in_gb_shadow"] = (S / ws * (1 if mc is not None and ws > 2 else (ws - 1)) + 1.5 * S * (ws - 1) / ws) / 1e9
         res["nvlink_in_gb_allreduce"] = (S / ws + S * (ws - 1) / ws) / 1e9
+        sampler.__exit__()
+        res["clocks"] = sampler.summary()
         rows.append(res)
         if rank == 0:
             print(json.dumps(res), flush=True)
         del launch, fm, fv, m, v
     if rank == 0 and args.json:
         json.dump(rows, open(args.json, "w"), indent=1)
+    kernels.comm_check()
     dist.barrier()
     dist.destroy_process_group()
 

@@ -283,6 +283,38 @@ def xent_bwd(logits2d: Tensor, targets: Tensor, lse: Tensor, dloss: Tensor, out:
 
 
 # ------------------------------------------------------------------------------------------------
+# row softmax
+# ------------------------------------------------------------------------------------------------
+def softmax_rows(x2d: Tensor, out_dtype: torch.dtype | None = None, scale: float = 1.0, causal_period: int = 0,
+                 out: Tensor | None = None) -> Tensor:
+    """``softmax(scale * x2d)`` along the last dim of a 2-D tensor with unit inner stride; ``causal_period`` = N masks
+    row ``r`` (query ``r % N``) to columns ``0..r % N``."""
+    assert x2d.dim() == 2 and x2d.stride(1) == 1 and x2d.dtype in _DT
+    rows, cols = x2d.shape
+    out_dtype = out_dtype or x2d.dtype
+    if out is None:
+        out = torch.empty(rows, cols, dtype=out_dtype, device=x2d.device)
+    assert out.shape == x2d.shape and out.stride(1) == 1 and out.dtype == out_dtype
+    check(_lib().b200_softmax_rows(p(x2d), c_int(_DT[x2d.dtype]), p(out), c_int(_DT[out_dtype]), c_longlong(rows),
+                                   c_int(cols), c_longlong(x2d.stride(0)), c_longlong(out.stride(0)), c_float(scale),
+                                   c_int(causal_period), stream_ptr()), "softmax_rows")
+    _count()
+    return out
+
+
+def softmax_bwd_rows(prob: Tensor, dprob: Tensor, scale: float = 1.0, out: Tensor | None = None) -> Tensor:
+    """``scale * p * (dp - rowsum(dp * p))`` for contiguous 2-D ``p`` / ``dp`` of the same dtype (may run in place)."""
+    assert prob.shape == dprob.shape and prob.dtype == dprob.dtype and prob.is_contiguous() and dprob.is_contiguous()
+    rows, cols = prob.shape
+    if out is None:
+        out = torch.empty_like(prob)
+    check(_lib().b200_softmax_bwd_rows(p(prob), p(dprob), p(out), c_int(_DT[prob.dtype]), c_longlong(rows), c_int(cols),
+                                       c_longlong(cols), c_float(scale), stream_ptr()), "softmax_bwd_rows")
+    _count()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
 # multi-tensor AdamW / clipping
 # ------------------------------------------------------------------------------------------------
 class _AdamWTensor(ctypes.Structure):
@@ -328,6 +360,9 @@ class AdamWLaunch:
 
     def __init__(self, params, grads, ms, vs, shadows, step0: int, mode: int = 0):
         self.tt = TensorTable(params, grads, ms, vs, shadows)
+        # the table stores raw addresses: keep every tensor alive for as long as the launch object exists
+        self._keepalive = (list(params), list(grads), list(ms) if ms is not None else None,
+                           list(vs) if vs is not None else None, list(shadows) if shadows is not None else None)
         dev = self.tt.device
         self.hyper = torch.zeros(8, dtype=torch.float32, device=dev)
         # ring of pinned staging rows: the host may run several steps ahead of the async copies
@@ -340,6 +375,11 @@ class AdamWLaunch:
     def set_hyper(self, lr, b1, b2, eps, wd, grad_scale=1.0) -> None:
         vals = (float(lr), float(b1), float(b2), float(eps), float(wd), float(grad_scale))
         if vals == self._hyper_vals:
+            return
+        if self.hyper.is_cuda and torch.cuda.is_current_stream_capturing():
+            # a copy recorded into a CUDA graph would overwrite the refreshed values on every replay with whatever
+            # this staging row holds by then; leave the device copy alone (the trainer pushes pending values with
+            # refresh_device_hyper() right before capturing and before every replay)
             return
         self._hyper_vals = vals
         row = self._hyper_host[self._hyper_slot]
@@ -357,11 +397,29 @@ class AdamWLaunch:
         bump_param_epoch()
 
 
+_clip_plans: dict = {}
+
+
 def clip_grad_norm(grads: list[Tensor], max_norm: float, eps: float, table: TensorTable | None = None) -> Tensor:
-    tt = table or TensorTable([None] * len(grads), grads)
-    nparts = _lib().b200_gradnorm_partials(c_longlong(tt.total_chunks))
-    partial = torch.empty(nparts, dtype=torch.float32, device=tt.device)
-    out = torch.empty(2, dtype=torch.float32, device=tt.device)
+    """Global-L2 clip of contiguous fp32 ``grads`` in place (3 launches).  The descriptor table, the partial-sum
+    buffer and the result are built once per set of gradient addresses and reused (arena-backed gradients keep
+    their addresses), so steady-state calls neither allocate nor copy from the host — which is also what lets a
+    clipped step be captured in a CUDA graph."""
+    key = tuple((g.data_ptr(), g.numel()) for g in grads)
+    plan = None if table is not None else _clip_plans.get(key)
+    if plan is None:
+        if table is None and torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("clip_grad_norm: first call for this set of gradients must happen before stream "
+                               "capture (it builds the descriptor table with a host-to-device copy)")
+        tt = table or TensorTable([None] * len(grads), grads)
+        nparts = _lib().b200_gradnorm_partials(c_longlong(tt.total_chunks))
+        plan = (tt, torch.empty(nparts, dtype=torch.float32, device=tt.device),
+                torch.empty(2, dtype=torch.float32, device=tt.device), list(grads))
+        if table is None:
+            if len(_clip_plans) >= 8:
+                _clip_plans.pop(next(iter(_clip_plans)))
+            _clip_plans[key] = plan
+    tt, partial, out, _keep = plan
     check(_lib().b200_clip_grad_norm(p(tt.table), p(tt.starts), c_int(tt.n), c_longlong(tt.total_chunks),
                                      c_float(max_norm), c_float(eps), p(partial), p(out), c_int(1), stream_ptr()),
           "clip_grad_norm")
@@ -377,19 +435,41 @@ def _strides3(t: Tensor):
     return (c_longlong * 3)(t.stride(0), t.stride(1), t.stride(2))
 
 
-def fa2_fwd(q: Tensor, k: Tensor, v: Tensor, causal: bool, out: Tensor | None = None):
+def cast3_bf16(a: Tensor, b: Tensor | None = None, c: Tensor | None = None):
+    """bf16 copies of up to three contiguous fp32 tensors in ONE launch."""
+    srcs = [t for t in (a, b, c) if t is not None]
+    for t in srcs:
+        assert t.dtype == torch.float32 and t.is_contiguous()
+    outs = [torch.empty(t.shape, dtype=torch.bfloat16, device=t.device) for t in srcs]
+    args = []
+    for i in range(3):
+        if i < len(srcs):
+            args += [p(srcs[i]), p(outs[i]), c_longlong(srcs[i].numel())]
+        else:
+            args += [c_void_p(0), c_void_p(0), c_longlong(0)]
+    check(_lib().b200_cast3_f32_to_bf16(*args, stream_ptr()), "cast3")
+    _count()
+    return outs
+
+
+def fa2_fwd(q: Tensor, k: Tensor, v: Tensor, causal: bool, out: Tensor | None = None, out_f32: bool = False,
+            cluster: bool = True):
     """``q,k,v``: bf16 ``(B, H, N, D)`` views (any batch/head/row strides).  Returns ``(o, lse)``;
-    ``o`` has q's layout unless ``out`` is given, ``lse`` is fp32 ``(B, H, Nq)``."""
+    ``o`` has q's layout unless ``out`` is given (bf16, or fp32 with ``out_f32``), ``lse`` is fp32 ``(B, H, Nq)``.
+    ``cluster``: let pairs of CTAs share K/V tiles through TMA multicast when the query-tile count is even."""
     B, H, Nq, D = q.shape
     Nk = k.shape[2]
     assert q.dtype == k.dtype == v.dtype == torch.bfloat16
+    odt = torch.float32 if out_f32 else torch.bfloat16
     if out is None:
-        out = torch.empty_strided(q.shape, q.stride(), dtype=torch.bfloat16, device=q.device) \
-            if q.is_contiguous() else torch.empty(B, Nq, H, D, dtype=torch.bfloat16, device=q.device).permute(0, 2, 1, 3)
+        out = torch.empty_strided(q.shape, q.stride(), dtype=odt, device=q.device) \
+            if q.is_contiguous() else torch.empty(B, Nq, H, D, dtype=odt, device=q.device).permute(0, 2, 1, 3)
+    assert out.dtype == odt
     lse = torch.empty(B, H, Nq, dtype=torch.float32, device=q.device)
-    check(_lib().b200_fa2_fwd(p(q), p(k), p(v), p(out), p(lse), c_int(B), c_int(H), c_int(Nq), c_int(Nk), c_int(D),
-                              _strides3(q), _strides3(k), _strides3(v), _strides3(out), c_int(int(causal)),
-                              c_float(1.0 / (D ** 0.5)), stream_ptr()), "fa2_fwd")
+    check(_lib().b200_fa2_fwd_ex(p(q), p(k), p(v), p(out), p(lse), c_int(B), c_int(H), c_int(Nq), c_int(Nk), c_int(D),
+                                 _strides3(q), _strides3(k), _strides3(v), _strides3(out), c_int(int(causal)),
+                                 c_float(1.0 / (D ** 0.5)), c_int(int(out_f32)), c_int(int(cluster)), stream_ptr()),
+          "fa2_fwd")
     _count()
     return out, lse
 
@@ -397,15 +477,19 @@ def fa2_fwd(q: Tensor, k: Tensor, v: Tensor, causal: bool, out: Tensor | None = 
 _dq_workspaces: dict = {}
 
 
-def fa2_bwd(q, k, v, o, lse, do, causal: bool, dq=None, dk=None, dv=None, rope_cache: Tensor | None = None):
-    """``rope_cache``: when q,k were rotated before attention, un-rotate dq,dk on the way out (fused)."""
+def fa2_bwd(q, k, v, o, lse, do, causal: bool, dq=None, dk=None, dv=None, rope_cache: Tensor | None = None,
+            grads_f32: bool = False):
+    """``rope_cache``: when q,k were rotated before attention, un-rotate dq,dk on the way out (fused).
+    ``o`` / ``do`` may be fp32 (the delta pre-pass reads them as they are and emits the bf16 ``do`` the tensor cores
+    need); ``grads_f32`` makes the kernels write fp32 dq/dk/dv."""
     B, H, Nq, D = q.shape
     Nk = k.shape[2]
     if do.stride(3) != 1:
         do = do.contiguous()
-    dq = torch.empty_like(q) if dq is None else dq
-    dk = torch.empty_like(k) if dk is None else dk
-    dv = torch.empty_like(v) if dv is None else dv
+    gdt = torch.float32 if grads_f32 else q.dtype
+    dq = torch.empty(q.shape, dtype=gdt, device=q.device) if dq is None else dq
+    dk = torch.empty(k.shape, dtype=gdt, device=q.device) if dk is None else dk
+    dv = torch.empty(v.shape, dtype=gdt, device=q.device) if dv is None else dv
     delta = torch.empty(B, H, Nq, dtype=torch.float32, device=q.device)
     # fp32 dQ accumulator: one zeroed workspace per shape, handed back zeroed by the kernel's last pass
     # (calls of the same shape are assumed to be stream-ordered, as they are in a training step)
@@ -418,11 +502,13 @@ def fa2_bwd(q, k, v, o, lse, do, causal: bool, dq=None, dk=None, dv=None, rope_c
     if rope_cache is not None:
         assert rope_cache.dtype == torch.float32 and rope_cache.is_contiguous() and rope_cache.shape[2] * 2 == D
         rope_ctx = rope_cache.shape[1]
+    flags = 1 | (2 if o.dtype == torch.float32 else 0) | (4 if do.dtype == torch.float32 else 0) | (8 if grads_f32 else 0)
+    do_scratch = torch.empty(B, H, Nq, D, dtype=torch.bfloat16, device=q.device) if do.dtype == torch.float32 else None
     check(_lib().b200_fa2_bwd_ex(p(q), p(k), p(v), p(o), p(lse), p(do), p(dq), p(dk), p(dv), p(delta), p(dq_acc),
                                    c_int(B), c_int(H), c_int(Nq), c_int(Nk), c_int(D), _strides3(q), _strides3(k),
                                    _strides3(v), _strides3(o), _strides3(do), _strides3(dq), _strides3(dk),
                                    _strides3(dv), c_int(int(causal)), c_float(1.0 / (D ** 0.5)), p(rope_cache),
-                                   c_int(rope_ctx), c_int(1), stream_ptr()), "fa2_bwd")
+                                   c_int(rope_ctx), c_int(flags), p(do_scratch), stream_ptr()), "fa2_bwd")
     _count(4)
     return dq, dk, dv
 
@@ -465,6 +551,40 @@ def bcast_pull(arena, byte_off: int, nbytes: int, src: int, signal_slot: int = 0
                                  c_int(src), c_int(arena.rank), c_int(arena.world_size), c_int(0),
                                  c_int(signal_slot), stream_ptr()), "bcast_pull")
     _count()
+
+
+def bcast_mc(arena, byte_off: int, nbytes: int, src: int, signal_slot: int = 0) -> None:
+    """Rank ``src`` stores ``nbytes`` at ``byte_off`` of its arena into every rank's arena through the NVLS multicast
+    mapping (one kernel; needs ``arena.multicast_ptr``)."""
+    check(_lib().b200_bcast_mc(arena.peer_ptrs_c, arena.signal_ptrs_c, c_void_p(arena.multicast_ptr),
+                               c_longlong(byte_off), c_longlong(nbytes), c_int(src), c_int(arena.rank),
+                               c_int(arena.world_size), c_int(0), c_int(signal_slot), stream_ptr()), "bcast_mc")
+    _count()
+
+
+def comm_status() -> tuple | None:
+    """None when the NVLink kernels on the current device are healthy; else ``(rank, cta, peer, phase, slot, flag)`` of
+    the first cross-rank barrier that ran out of time (phase 1: raising the peer's flag, 2: waiting for the peer)."""
+    info = (c_int * 6)()
+    rc = _lib().b200_comm_status(info)
+    if rc == 0:
+        return None
+    if rc != 1:
+        check(rc, "comm_status")
+    return tuple(int(x) for x in info)
+
+
+def comm_check() -> None:
+    st = comm_status()
+    if st is not None:
+        raise RuntimeError("NVLink communicator dead: rank %d CTA %d gave up on peer %d (phase %d, signal slot %d, "
+                           "flag %d) — a rank died, fell behind by more than the barrier time limit, or ranks "
+                           "disagree on the kernel sequence" % st)
+
+
+def comm_reset(timeout_ms: int = 0) -> None:
+    """Clear the health block and (``timeout_ms`` > 0) set the cross-rank barrier time limit on the current device."""
+    check(_lib().b200_comm_reset(c_longlong(int(timeout_ms))), "comm_reset")
 
 
 def symm_barrier(arena, signal_slot: int) -> None:

@@ -386,10 +386,85 @@ def cross_entropy(logits: Tensor, targets: Tensor) -> Tensor:
 
 
 # ------------------------------------------------------------------------------------------------
+# row softmax, materialised attention (comparison arm of the attention benchmarks)
+# ------------------------------------------------------------------------------------------------
+class SoftmaxFn(torch.autograd.Function):
+    """Softmax over the last dimension on the row kernel (``csrc/softmax.cu``)."""
+
+    @staticmethod
+    def forward(ctx, x: Tensor):
+        x2 = x.reshape(-1, x.shape[-1])
+        if x2.stride(1) != 1:
+            x2 = x2.contiguous()
+        y = kernels.softmax_rows(x2)
+        ctx.save_for_backward(y)
+        return y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy: Tensor):
+        (y,) = ctx.saved_tensors
+        dy2 = dy.reshape(y.shape).to(y.dtype).contiguous()
+        return kernels.softmax_bwd_rows(y, dy2).view(dy.shape)
+
+
+def softmax_lastdim(x: Tensor) -> Tensor:
+    return SoftmaxFn.apply(x)
+
+
+class MaterializedAttentionFn(torch.autograd.Function):
+    """Attention that materialises the ``N_q x N_k`` probabilities, on this library's kernels: per batch element
+    ``S = Q Kᵀ`` (tcgen05 GEMM), one fused scale + causal-mask + softmax row kernel, ``O = P V`` (GEMM); backward =
+    four GEMMs and the softmax-backward row kernel.  The counterpart of what the reference's eager / ``torch.compile``d
+    ``scaled_dot_product_attention`` executes (``model.py:400-432``, ``benchmark_attention.py:113-201``); it is the
+    O(N²)-memory arm FlashAttention is compared against, not a path the LM uses."""
+
+    @staticmethod
+    def forward(ctx, q: Tensor, k: Tensor, v: Tensor, is_causal: bool = False):
+        B, Nq, D = q.shape
+        Nk = k.shape[1]
+        if q.dtype == torch.float32:
+            qb, kb, vb = kernels.cast3_bf16(q.contiguous(), k.contiguous(), v.contiguous())
+        else:
+            qb, kb, vb = q.contiguous(), k.contiguous(), v.contiguous()
+        scale = 1.0 / (D ** 0.5)
+        P = torch.empty(B, Nq, Nk, dtype=BF16, device=q.device)
+        O = torch.empty(B, Nq, D, dtype=BF16, device=q.device)
+        for b in range(B):
+            kernels.gemm(qb[b], kb[b], out=P[b])                                     # S (bf16) into P's storage
+            kernels.softmax_rows(P[b], scale=scale, causal_period=Nq if is_causal else 0, out=P[b])
+            kernels.gemm(P[b], vb[b], b_mn=True, out=O[b])
+        ctx.save_for_backward(qb, kb, vb, P)
+        ctx.scale = scale
+        ctx.in_dtype = q.dtype
+        return O.to(q.dtype) if q.dtype != BF16 else O
+
+    @staticmethod
+    def backward(ctx, dO: Tensor):
+        qb, kb, vb, P = ctx.saved_tensors
+        B, Nq, D = qb.shape
+        dOb = dO.to(BF16).contiguous()
+        dq, dk, dv = torch.empty_like(qb), torch.empty_like(kb), torch.empty_like(vb)
+        dP = torch.empty_like(P[0])
+        for b in range(B):
+            kernels.gemm(P[b], dOb[b], a_mn=True, b_mn=True, out=dv[b])             # dV = Pᵀ dO
+            kernels.gemm(dOb[b], vb[b], out=dP)                                      # dP = dO Vᵀ
+            kernels.softmax_bwd_rows(P[b], dP, scale=ctx.scale, out=dP)              # dS (scaled), in place
+            kernels.gemm(dP, kb[b], b_mn=True, out=dq[b])                            # dQ = dS K
+            kernels.gemm(dP, qb[b], a_mn=True, b_mn=True, out=dk[b])                 # dK = dSᵀ Q
+        dt = ctx.in_dtype
+        return dq.to(dt), dk.to(dt), dv.to(dt), None
+
+
+def materialized_attention(q: Tensor, k: Tensor, v: Tensor, is_causal: bool = False) -> Tensor:
+    return MaterializedAttentionFn.apply(q, k, v, is_causal)
+
+
+# ------------------------------------------------------------------------------------------------
 # optimizer-side helpers
 # ------------------------------------------------------------------------------------------------
 def clip_grad_norm_(grads: list[Tensor], max_norm: float, eps: float = 1e-6) -> Tensor:
-    return kernels.clip_grad_norm([g.contiguous() if not g.is_contiguous() else g for g in grads], max_norm, eps)
+    assert all(g.is_contiguous() for g in grads), "native clip needs contiguous gradients (api.clip_gradient checks)"
+    return kernels.clip_grad_norm(list(grads), max_norm, eps)
 
 
 class AdamWPlan:
@@ -398,6 +473,7 @@ class AdamWPlan:
     def __init__(self, params, grads, ms, vs, key, step0: int, mode: int = 0):
         self.key = key
         self.params = list(params)
+        self.host_step = step0  # the host's idea of the device step counter (see AdamW._step_fused)
         flat_p, flat_g, flat_m, flat_v, flat_s = [], [], [], [], []
         self._extra_shadows = []
         for p_, g_, m_, v_ in zip(params, grads, ms, vs):

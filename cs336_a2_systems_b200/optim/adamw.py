@@ -65,9 +65,14 @@ class AdamW(torch.optim.Optimizer):
         m = b1 * m + (1 - b1) * g
         v = b2 * v + (1 - b2) * torch.square(g)
         alpha_t = lr * (math.sqrt(1 - b2 ** t) / (1 - b1 ** t))
-        p.data -= alpha_t * m / (torch.sqrt(v) + eps)
-        p.data -= lr * wd * p.data
+        # in place on the parameter itself (callers hold no_grad): unlike ``p.data -= ...`` this bumps
+        # ``p._version``, which is what tells the bf16 weight-shadow cache (ops/native.py) to re-cast
+        p.sub_(alpha_t * m / (torch.sqrt(v) + eps))
+        p.sub_(lr * wd * p)
         state["m"], state["v"], state["t"] = m, v, t + 1
+        if p.is_cuda:
+            from ..ops import kernels
+            kernels.bump_param_epoch()
 
     def _fusable(self, p) -> bool:
         if self._fused is False or _native.force_torch():
@@ -133,7 +138,12 @@ class AdamW(torch.optim.Optimizer):
                 st["v"] = torch.zeros_like(p, memory_format=torch.preserve_format)
                 st["t"] = 1
         plan = self._plans.get(gi)
-        key = tuple((p.data_ptr(), p.grad.data_ptr()) for p in ps)
+        # the plan holds raw pointers: any replaced tensor (new grads, moments swapped in by load_state_dict) or a
+        # step counter that no longer matches the device copy (state restored to an earlier step) rebuilds it
+        key = tuple((p.data_ptr(), p.grad.data_ptr(), self.state[p]["m"].data_ptr(), self.state[p]["v"].data_ptr())
+                    for p in ps)
+        if plan is not None and plan.key == key and plan.host_step != self.state[ps[0]]["t"]:
+            plan = None
         if plan is None or plan.key != key:
             t0 = self.state[ps[0]]["t"]
             if any(self.state[p]["t"] != t0 for p in ps):
@@ -148,6 +158,20 @@ class AdamW(torch.optim.Optimizer):
         plan.launch(max_blocks)
         for p in ps:  # host mirror of the device step counter (exact outside CUDA-graph replay)
             self.state[p]["t"] += 1
+        plan.host_step = self.state[ps[0]]["t"]
+
+    def load_state_dict(self, state_dict) -> None:
+        """Restoring state replaces the moment tensors and step counters the fused plans point at: drop the plans so
+        the next step rebuilds them around the restored tensors (and a device step counter equal to the restored t)."""
+        super().load_state_dict(state_dict)
+        self._plans.clear()
+        self._done.clear()
+
+    def __setstate__(self, state) -> None:
+        super().__setstate__(state)
+        self.__dict__.setdefault("_fused", None)
+        self.__dict__["_plans"] = {}
+        self.__dict__["_done"] = set()
 
     def refresh_device_hyper(self) -> None:
         """Push the current ``lr`` / ``betas`` / ``eps`` / ``weight_decay`` of every param group to the device copies the
@@ -165,3 +189,4 @@ class AdamW(torch.optim.Optimizer):
             t = plan.device_step()
             for p in plan.params:
                 self.state[p]["t"] = t
+            plan.host_step = t

@@ -86,6 +86,9 @@ class _DDPBase(nn.Module):
         self.module = module
         self.process_group = process_group
         self.rank, self.world_size = world()
+        #: True once an optimizer path that consumes the gradients inside its own reduction has been attached
+        #: (ShardedOptimizer.enable_symmetric): ``param.grad`` then holds this rank's local gradient, not the average
+        self.grads_are_local = False
         broadcast_parameters(module, 0, process_group, buffers=broadcast_buffers)
         self._trainable = [p for p in _unique_params(module) if p.requires_grad]
 
@@ -197,7 +200,7 @@ class DDPBucketed(_DDPBase):
         # in-bucket slot order: forward parameter order; opt-in (B200SYS_FUSE_W13_WGRAD=1, not yet timed on hardware)
         # the fusion-friendly order that also puts w3 next to w1, so the SwiGLU pair gets ONE wgrad GEMM and — under
         # the bucket-fused optimizer — an arena-resident bf16 shadow instead of a per-step re-cast
-        if os.environ.get("B200SYS_FUSE_W13_WGRAD", "0") == "1":
+        if os.environ.get("B200SYS_FUSE_W13_WGRAD", "1") == "1":
             slot_pos = {id(p): k for k, p in enumerate(grad_slots.fusion_friendly_order(module))}
         else:
             slot_pos = {id(p): k for k, p in enumerate(module.parameters())}

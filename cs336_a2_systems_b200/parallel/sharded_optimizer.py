@@ -82,6 +82,12 @@ class ShardedOptimizer(torch.optim.Optimizer):
         self._distribute()
         return loss
 
+    def sync_params(self) -> None:
+        """Collective.  Bring every fp32 parameter replica up to date (only does work when the bucket-fused path runs
+        with a deferred fp32 gather); ordered before later work on the current stream."""
+        if self._symm is not None and hasattr(self._symm, "sync_params"):
+            self._symm.sync_params()
+
     def refresh_device_hyper(self) -> None:
         """Before a CUDA-graph replay: hand the current hyper-parameters to whatever fused path is active."""
         if self._symm is not None and hasattr(self._symm, "refresh_device_hyper"):
@@ -136,9 +142,20 @@ class ShardedOptimizer(torch.optim.Optimizer):
         return dist.get_global_rank(self.process_group, group_rank)
 
     # ------------------------------------------------------------------ NVLink fused path
-    def enable_symmetric(self, module: torch.nn.Module | None = None) -> bool:
+    def enable_symmetric(self, module: torch.nn.Module | None = None, defer_fp32_gather: bool | None = None,
+                         variant: int | None = None) -> bool:
         """Move parameters into a symmetric arena and fuse AdamW + distribution (see module doc).
-        Returns False (and changes nothing) when the path is not legal for this setup."""
+        Returns False (and changes nothing) when the path is not legal for this setup.
+
+        With a ``DDPBucketed`` module on the NVLink backend this selects the bucket-fused ZeRO-1 step
+        (``parallel/zero.py``), which differs from the reference's wrapper in ways a caller can observe: after
+        ``backward()`` ``param.grad`` holds this rank's LOCAL gradient (the average only ever exists as 1/world_size
+        slices inside the kernel; ``module.grads_are_local`` is set), the update is applied per bucket during
+        backward (so global gradient-norm clipping is refused by ``Trainer``), and a single param group is required.
+        ``defer_fp32_gather=True`` additionally postpones the fp32 replicas of Linear weights to the next forward /
+        ``sync_params()`` (see ``parallel/zero.py``); ``variant`` picks the kernel (bit 0: gradients reduced in the
+        NVSwitch, bit 1: stores replicated by the switch; default by world size).  Not calling this keeps the
+        reference semantics."""
         from . import symm_optimizer
 
         red = getattr(module, "_reducer", None)
@@ -148,7 +165,8 @@ class ShardedOptimizer(torch.optim.Optimizer):
             # DDPBucketed on the NVLink backend: fuse reduce-scatter + sharded AdamW + all-gather per bucket
             from .zero import BucketFusedAdamW
 
-            self._symm = BucketFusedAdamW(self, module, mode)
+            self._symm = BucketFusedAdamW(self, module, mode, defer_fp32_gather, variant)
+            module.grads_are_local = True
             return True
         s = symm_optimizer.try_make(self, module)
         self._symm = s
@@ -202,3 +220,6 @@ class ShardedOptimizer(torch.optim.Optimizer):
             if self._owner[id(p)] != self.rank:
                 continue
             self.optimizer.state[p] = {k: (v.to(p.device) if torch.is_tensor(v) else v) for k, v in st.items()}
+        plans = getattr(self.optimizer, "_plans", None)
+        if plans is not None:  # fused launch plans hold the replaced moment tensors' addresses
+            plans.clear()

@@ -72,7 +72,7 @@ class SymmArena:
         self.world_size = dist.get_world_size(self.group)
         nbytes = (nbytes + 255) // 256 * 256
         if symm_mem.get_signal_pad_size() < 16384:
-            symm_mem.set_signal_pad_size(16384)  # room for two slots of 64 blocks x 8 ranks flag words
+            symm_mem.set_signal_pad_size(16384)  # room for two slots of 148 CTAs x 8 ranks flag words (9472 bytes)
         self.bytes = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
         self.bytes.zero_()
         self.handle = symm_mem.rendezvous(self.bytes, self.group.group_name)
@@ -163,8 +163,9 @@ class SymmReducer:
 
 @torch.no_grad()
 def broadcast_tensors(tensors, src: int, group=None) -> None:
-    """Make ``tensors`` (same device, any dtypes) equal to rank ``src``'s copies with ONE NVLink pull kernel over a
-    packed symmetric staging buffer (the reference issues one NCCL broadcast per parameter)."""
+    """Make ``tensors`` (same device, any dtypes) equal to rank ``src``'s copies with ONE NVLink kernel over a packed
+    symmetric staging buffer (the reference issues one NCCL broadcast per parameter): a multicast store through the
+    switch when the arena has an NVLS mapping (the source sends the bytes once), else every other rank pulls."""
     from ..ops import kernels
 
     if not tensors:
@@ -179,7 +180,10 @@ def broadcast_tensors(tensors, src: int, group=None) -> None:
     if arena.rank == src:
         for v, t in zip(views, tensors):
             v.copy_(t)
-    kernels.bcast_pull(arena, 0, off, src)
+    if arena.multicast_ptr and os.environ.get("B200SYS_BCAST", "mc") != "pull":
+        kernels.bcast_mc(arena, 0, off, src)
+    else:
+        kernels.bcast_pull(arena, 0, off, src)
     if arena.rank != src:
         for v, t in zip(views, tensors):
             t.copy_(v)

@@ -113,7 +113,7 @@ class _OptimizerOverlap:
 class Trainer:
     def __init__(self, model: torch.nn.Module, optimizer: torch.optim.Optimizer, *, autocast: bool = True,
                  max_grad_norm: float | None = None, cuda_graph: bool = False, grad_arena: bool | None = None,
-                 overlap_optimizer: bool = False, overlap_unit_mb: float = 128.0):
+                 overlap_optimizer: bool = False, overlap_unit_mb: float = 128.0, graph_warmup_steps: int = 3):
         self.model = model
         self.optimizer = optimizer
         self.autocast = autocast
@@ -132,7 +132,7 @@ class Trainer:
         self.arena = None
         if grad_arena or (grad_arena is None and self.device.type == "cuda" and not self._is_ddp):
             # opt-in (not yet timed on hardware): lay w3's slot next to w1's so their wgrads become ONE GEMM
-            fuse_w13 = os.environ.get("B200SYS_FUSE_W13_WGRAD", "0") == "1"
+            fuse_w13 = os.environ.get("B200SYS_FUSE_W13_WGRAD", "1") == "1"
             self.arena = GradArena(grad_slots.fusion_friendly_order(model) if fuse_w13 else list(model.parameters()))
         self._overlap = None
         if overlap_optimizer and self.device.type == "cuda" and max_grad_norm is None and \
@@ -141,6 +141,11 @@ class Trainer:
         self._graph = None
         self._static_x = self._static_y = self._static_loss = None
         self._warm_steps = 0
+        #: eager steps before the capture (>= 1: optimizer plans, weight shadows and allocator pools must exist)
+        self.graph_warmup_steps = max(1, int(graph_warmup_steps))
+        #: kernels of the native library recorded into the step graph / number of replays so far (bench accounting)
+        self.graph_kernel_count = 0
+        self.graph_replays = 0
         self.steps_done = 0
 
     # ------------------------------------------------------------------ one eager step
@@ -178,11 +183,18 @@ class Trainer:
         self._graph = torch.cuda.CUDAGraph()
         # private side stream for capture, as torch requires
         s = torch.cuda.Stream(device=self.device)
+        # push pending hyper-parameter changes (LR schedule) to the device NOW: inside the capture the optimizers
+        # refuse to copy, because a recorded copy would be replayed with stale staging contents on every step
+        refresh = getattr(self.optimizer, "refresh_device_hyper", None)
+        if refresh is not None:
+            refresh()
         s.wait_stream(torch.cuda.current_stream(self.device))
+        n0 = kernels_mod.native_launches()
         with torch.cuda.stream(s):
             self.optimizer.zero_grad(set_to_none=True)
             with torch.cuda.graph(self._graph, stream=s):
                 self._static_loss = self._step_eager(self._static_x, self._static_y)
+        self.graph_kernel_count = kernels_mod.native_launches() - n0
         torch.cuda.current_stream(self.device).wait_stream(s)
 
     def step(self, x: Tensor, y: Tensor) -> Tensor:
@@ -191,7 +203,7 @@ class Trainer:
         if not self.cuda_graph or self.device.type != "cuda":
             return self._step_eager(x, y)
         if self._graph is None:
-            if self._warm_steps < 3:  # plans, shadows and allocator pools must exist before capture
+            if self._warm_steps < self.graph_warmup_steps:  # plans, shadows and allocator pools must exist before capture
                 self._warm_steps += 1
                 return self._step_eager(x, y)
             self._capture(x, y)
@@ -202,6 +214,7 @@ class Trainer:
         if refresh is not None:  # LR schedules: the replay reads lr / betas / ... from device memory
             refresh()
         self._graph.replay()
+        self.graph_replays += 1
         kernels_mod.bump_param_epoch()  # the replayed optimizer kernels rewrote the parameters
         return self._static_loss
 

@@ -75,3 +75,30 @@ def max_over_ranks(value: float, device=None) -> float:
     t = torch.tensor([value], dtype=torch.float64, device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
+
+
+def time_collective(fn: Callable[[], object], warmup: int, iters: int, dev, min_seconds: float = 0.25) -> float:
+    """Per-call device time (ms) of a multi-rank ``fn``: CUDA events around batches of ``iters`` calls, batches
+    repeated until ``min_seconds`` of device time have been timed (long enough for ``nvidia-smi`` to sample the
+    clocks of the region), median batch, max over ranks."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize(dev)
+    if dist.is_available() and dist.is_initialized():
+        dist.barrier()
+    per_call, total = [], 0.0
+    while total < min_seconds * 1e3 and len(per_call) < 50:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize(dev)
+        ms = e0.elapsed_time(e1)
+        per_call.append(ms / iters)
+        # every rank must run the same number of batches of the same size: agree on the elapsed time
+        agreed = max_over_ranks(ms, dev)
+        total += agreed
+        if agreed < 5.0:
+            iters *= 4  # microsecond-scale calls: grow the batch instead of the batch count
+    return max_over_ranks(statistics.median(per_call), dev)

@@ -19,43 +19,23 @@
 // fixed (rank 0..ws-1, or the switch's), and each element is produced by exactly one rank in the
 // two-shot / multimem variants, so all replicas end bit-identical.
 #include "common.cuh"
+#include "comm_barrier.cuh"
 
 namespace b200 {
 namespace comm {
 
-constexpr int kMaxRanks = 8;
 constexpr int kThreads = 512;
 constexpr int kMaxBlocks = 64;
+static_assert(kMaxBlocks <= kSignalBlocks, "a signal slot holds kSignalBlocks CTAs' flag words");
 
 struct Peers {
   void* ptr[kMaxRanks];
   unsigned int* sig[kMaxRanks];
 };
 
-__device__ __forceinline__ unsigned cas_release_sys(unsigned* addr, unsigned cmp, unsigned val) {
-  unsigned old;
-  asm volatile("atom.global.release.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(addr), "r"(cmp), "r"(val) : "memory");
-  return old;
-}
-__device__ __forceinline__ unsigned cas_acquire_sys(unsigned* addr, unsigned cmp, unsigned val) {
-  unsigned old;
-  asm volatile("atom.global.acquire.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(addr), "r"(cmp), "r"(val) : "memory");
-  return old;
-}
-
-// CTA-to-CTA barrier across ranks (same blockIdx on every rank).  Reusable: every flag returns to 0.
+// CTA-to-CTA barrier across ranks (same blockIdx on every rank), bounded spin: see comm_barrier.cuh.
 __device__ __forceinline__ void cross_rank_barrier(const Peers& P, int rank, int ws, int slot) {
-  __syncthreads();
-  if (threadIdx.x < ws) {
-    const int peer = threadIdx.x;
-    unsigned* send = P.sig[peer] + slot + blockIdx.x * kMaxRanks + rank;
-    unsigned* recv = P.sig[rank] + slot + blockIdx.x * kMaxRanks + peer;
-    while (cas_release_sys(send, 0u, 1u) != 0u) {
-    }
-    while (cas_acquire_sys(recv, 1u, 0u) != 1u) {
-    }
-  }
-  __syncthreads();
+  cross_rank_barrier(P.sig, rank, ws, slot);
 }
 
 __device__ __forceinline__ f32x4 ld_peer(const void* p) {
@@ -268,6 +248,32 @@ __global__ void __launch_bounds__(kThreads) bcast_pull_kernel(Peers P, long long
   cross_rank_barrier(P, rank, ws, slot);  // the source may reuse its buffer
 }
 
+// Broadcast by multicast store (NVLS): the source rank reads its own copy once and writes it through the switch
+// with multimem.st — the switch replicates every store into all ranks' arenas, so the source's NVLink egress is S
+// bytes instead of the (ws-1)·S that ws-1 pulling peers cost it.  Replaces one NCCL broadcast per parameter at DDP
+// construction (ddp_bucketed_overlapped_sharded.py:225-226,260-261).  Non-source ranks only take part in the barriers.
+__global__ void __launch_bounds__(kThreads) bcast_mc_kernel(Peers P, char* mc, long long byte_off, long long nvec16,
+                                                            int src, int rank, int ws, int slot) {
+  cross_rank_barrier(P, rank, ws, slot);  // nobody is still reading what is about to be overwritten
+  if (rank == src) {
+    const char* from = static_cast<const char*>(P.ptr[src]) + byte_off;
+    char* to = mc + byte_off;
+    const long long stride = (long long)gridDim.x * kThreads;
+    for (long long i0 = (long long)blockIdx.x * kThreads + threadIdx.x; i0 < nvec16; i0 += 4 * stride) {
+      f32x4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (i0 + u * stride < nvec16) v[u] = *reinterpret_cast<const f32x4*>(from + (i0 + u * stride) * 16);
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (i0 + u * stride < nvec16)
+          asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(to + (i0 + u * stride) * 16),
+                       "f"(v[u].x), "f"(v[u].y), "f"(v[u].z), "f"(v[u].w) : "memory");
+    }
+  }
+  cross_rank_barrier(P, rank, ws, slot);  // the stores have landed everywhere
+}
+
 static int load_peers(const unsigned long long* peer_ptrs_host, const unsigned long long* signal_ptrs_host, int ws,
                       Peers* out) {
   for (int r = 0; r < kMaxRanks; ++r) {
@@ -306,6 +312,7 @@ extern "C" int b200_allreduce(const unsigned long long* peer_ptrs_host, const un
   if (algo == 0) algo = nbytes <= 64 * 1024 ? 1 : ((multicast_ptr && world_size > 2) ? 3 : 2);
   if (algo == 1 && nvec > (long long)blocks * kThreads * kOneShotVecs) algo = 2;  // does not fit in registers
   if (algo == 3 && !multicast_ptr) algo = 2;
+  B200_REQUIRE(algo != 2 || byte_off % 32 == 0, "allreduce: the two-shot path moves 32-byte vectors; offset %lld is not 32-byte aligned", byte_off);
   const bool bf = dtype == B200_BF16;
   switch (algo) {
     case 1:
@@ -361,4 +368,48 @@ extern "C" int b200_bcast_pull(const unsigned long long* peer_ptrs_host, const u
   return 0;
 }
 
-extern "C" int b200_comm_signal_words(void) { return kMaxBlocks * kMaxRanks; }
+extern "C" int b200_bcast_mc(const unsigned long long* peer_ptrs_host, const unsigned long long* signal_ptrs_host,
+                             void* multicast_ptr, long long byte_off, long long nbytes, int src_rank, int rank,
+                             int world_size, int blocks, int signal_slot, void* stream) {
+  B200_REQUIRE(world_size >= 1 && world_size <= kMaxRanks, "bcast_mc: world size %d unsupported", world_size);
+  B200_REQUIRE(src_rank >= 0 && src_rank < world_size, "bcast_mc: bad source rank %d", src_rank);
+  B200_REQUIRE(byte_off % 16 == 0, "bcast_mc: offset must be 16-byte aligned");
+  B200_REQUIRE(multicast_ptr != nullptr, "bcast_mc: the arena has no NVLS multicast mapping (use b200_bcast_pull)");
+  if (nbytes <= 0) return 0;
+  Peers P;
+  if (int rc = load_peers(peer_ptrs_host, signal_ptrs_host, world_size, &P)) return rc;
+  if (blocks <= 0) blocks = 48;
+  if (blocks > kMaxBlocks) blocks = kMaxBlocks;
+  bcast_mc_kernel<<<blocks, kThreads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      P, static_cast<char*>(multicast_ptr), byte_off, (nbytes + 15) / 16, src_rank, rank, world_size, signal_slot);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+// 32-bit words of one signal slot: flag words for the largest grid any barrier-using kernel launches.
+extern "C" int b200_comm_signal_words(void) { return kSignalBlocks * kMaxRanks; }
+
+namespace b200 { namespace comm { int adamw_tu_status(CommStatus* out); int adamw_tu_reset(unsigned long long timeout_ns); } }
+
+// Health of the NVLink communicator on the current device: 0 = fine; 1 = a cross-rank barrier timed out (info[0..5] =
+// rank, CTA, peer, phase (1 = raising the peer's flag, 2 = waiting for the peer), signal slot, flag value seen) —
+// everything produced by comm kernels since then is invalid.  Synchronise the device (or the stream) first.
+extern "C" int b200_comm_status(int* info6) {
+  CommStatus st[2] = {};
+  B200_REQUIRE(comm_status_read(&st[0]) == 0, "comm_status: cannot read the status block");
+  B200_REQUIRE(adamw_tu_status(&st[1]) == 0, "comm_status: cannot read the status block");
+  for (int i = 0; i < 2; ++i)
+    if (st[i].dead) {
+      if (info6) { info6[0] = st[i].rank; info6[1] = st[i].block; info6[2] = st[i].peer; info6[3] = st[i].phase; info6[4] = st[i].slot; info6[5] = (int)st[i].flag; }
+      return 1;
+    }
+  return 0;
+}
+
+// Clears the status block and sets the barrier timeout (ms; 0 keeps the current value) on the current device.
+extern "C" int b200_comm_reset(long long timeout_ms) {
+  const unsigned long long ns = timeout_ms > 0 ? (unsigned long long)timeout_ms * 1000000ull : 0ull;
+  B200_REQUIRE(comm_status_reset_and_set_timeout(ns) == 0, "comm_reset: cudaMemcpyToSymbol failed");
+  B200_REQUIRE(adamw_tu_reset(ns) == 0, "comm_reset: cudaMemcpyToSymbol failed");
+  return 0;
+}

@@ -116,9 +116,57 @@ __global__ void cast_f32_bf16_kernel(const float* __restrict__ in, __nv_bfloat16
   }
 }
 
+// up to three fp32 -> bf16 casts in one launch (blockIdx.y picks the tensor): the q, k, v of an fp32 attention call
+struct Cast3 {
+  const float* in[3];
+  __nv_bfloat16* out[3];
+  size_t n[3];
+  bool aligned[3];
+};
+__global__ void cast3_f32_bf16_kernel(Cast3 c) {
+  const int t = blockIdx.y;
+  const float* __restrict__ in = c.in[t];
+  __nv_bfloat16* __restrict__ out = c.out[t];
+  const size_t n = c.n[t];
+  for (size_t i8 = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 8; i8 < n; i8 += (size_t)gridDim.x * blockDim.x * 8) {
+    if (c.aligned[t] && i8 + 7 < n) {
+      const f32x4 a = *reinterpret_cast<const f32x4*>(in + i8), b = *reinterpret_cast<const f32x4*>(in + i8 + 4);
+      *reinterpret_cast<u32x4*>(out + i8) =
+          u32x4{pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w)};
+    } else {
+      for (size_t i = i8; i < n && i < i8 + 8; ++i) out[i] = __float2bfloat16(in[i]);
+    }
+  }
+}
+
 }  // namespace b200
 
 using namespace b200;
+
+extern "C" int b200_cast3_f32_to_bf16(const float* in0, void* out0, long long n0, const float* in1, void* out1,
+                                      long long n1, const float* in2, void* out2, long long n2, void* stream) {
+  Cast3 c;
+  const float* ins[3] = {in0, in1, in2};
+  void* outs[3] = {out0, out1, out2};
+  const long long ns[3] = {n0, n1, n2};
+  long long nmax = 0;
+  int cnt = 0;
+  for (int t = 0; t < 3; ++t) {
+    if (ns[t] <= 0 || !ins[t]) break;
+    c.in[t] = ins[t];
+    c.out[t] = reinterpret_cast<__nv_bfloat16*>(outs[t]);
+    c.n[t] = (size_t)ns[t];
+    c.aligned[t] = ((reinterpret_cast<uintptr_t>(ins[t]) | reinterpret_cast<uintptr_t>(outs[t])) & 15) == 0;
+    nmax = ns[t] > nmax ? ns[t] : nmax;
+    ++cnt;
+  }
+  if (cnt == 0) return 0;
+  long long blocks = ((nmax + 7) / 8 + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  cast3_f32_bf16_kernel<<<dim3((unsigned)blocks, (unsigned)cnt), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(c);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
 
 extern "C" int b200_rope_qk_inplace(void* qkv_bf16, const float* cache, int ctx, int B, int S, int H, int dh,
                                     int inverse, void* stream) {

@@ -42,6 +42,17 @@ int b200_gemm_bf16_ex(const void* A, const void* B, void* C, const void* aux, in
                       int ldc, int ld_aux, int a_mn_major, int b_mn_major, int epilogue, int force_bn, int rope_S,
                       int rope_dh, int rope_cols, int rope_ctx, void* stream);
 
+/* ---- row softmax -------------------------------------------------------------------------------
+ * out[r, :] = softmax(scale * in[r, :]) for `rows` rows of `cols` columns (row strides ld_in / ld_out in elements;
+ * fp32 or bf16 in and out).  causal_period > 0: row r is query position r % causal_period and only sees columns
+ * 0..position; masked outputs are 0.  b200_softmax_bwd_rows: ds = scale * p * (dp - rowsum(dp * p)).
+ * ref: softmax (cs336_basics/nn_utils.py:4-7) and the where(mask, s, -inf) + softmax of the materialised
+ * attention (model.py:425-432). */
+int b200_softmax_rows(const void* in, int in_dtype, void* out, int out_dtype, long long rows, int cols,
+                      long long ld_in, long long ld_out, float scale, int causal_period, void* stream);
+int b200_softmax_bwd_rows(const void* p, const void* dp, void* ds, int dtype, long long rows, int cols, long long ld,
+                          float scale, void* stream);
+
 /* ---- FlashAttention-2 (tcgen05/TMEM/TMA) ------------------------------------------------------
  * q,k,v,o: bf16 with element strides (batch, head, row); last dim contiguous, D in {16,32,64,80,96,128}.
  * lse: fp32 [B,H,Nq] contiguous.  scale = 1/sqrt(D) is applied inside.
@@ -49,6 +60,12 @@ int b200_gemm_bf16_ex(const void* A, const void* B, void* C, const void* aux, in
 int b200_fa2_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int H, int Nq, int Nk,
                  int D, const long long* q_strides, const long long* k_strides, const long long* v_strides,
                  const long long* o_strides, int causal, float scale, void* stream);
+/* Extended form.  out_f32 = 1: o is fp32 (same element strides) — fp32 callers get an unrounded O and no cast pass.
+ * cluster = 1 (what b200_fa2_fwd uses): when the number of 128-row query tiles is even, pairs of CTAs form a
+ * thread-block cluster and share every K/V tile through TMA multicast; 0 = one independent CTA per query tile. */
+int b200_fa2_fwd_ex(const void* q, const void* k, const void* v, void* o, float* lse, int B, int H, int Nq, int Nk,
+                    int D, const long long* q_strides, const long long* k_strides, const long long* v_strides,
+                    const long long* o_strides, int causal, float scale, int out_f32, int cluster, void* stream);
 /* delta: fp32 [B,H,Nq] scratch (rowsum(O∘dO)); dq_acc: fp32 [B,H,Nq,D] scratch, zeroed inside.
  * dq,dk,dv: bf16 with their own strides.
  * ref: torch.compile'd backward_pass_recomp materialising N×N matrices (flash_attention.py:270-289). */
@@ -60,13 +77,16 @@ int b200_fa2_bwd(const void* q, const void* k, const void* v, const void* o, con
 
 /* Extended form: rope_cache (nullable, fp32 (2, rope_ctx, D/2)) = q,k were rotated before attention, so dq and dk are
  * un-rotated on the way out (fused into the fp32->bf16 pass of dq and the dK epilogue).  flags bit 0: dq_acc is
- * already all-zero and must be left all-zero (the convert pass re-zeroes it; saves a memset per call). */
+ * already all-zero and must be left all-zero (the convert pass re-zeroes it; saves a memset per call); bit 1: o is
+ * fp32; bit 2: dout is fp32 — do_bf16_scratch (B*H*Nq*D bf16) then receives its bf16 copy from the delta pre-pass;
+ * bit 3: dq, dk, dv are fp32 (not together with rope_cache).  The fp32 forms serve fp32 callers
+ * (reference tests/test_attention.py:29-40) without any separate cast kernel on the way in or out. */
 int b200_fa2_bwd_ex(const void* q, const void* k, const void* v, const void* o, const float* lse, const void* dout,
                     void* dq, void* dk, void* dv, float* delta, float* dq_acc, int B, int H, int Nq, int Nk, int D,
                     const long long* q_strides, const long long* k_strides, const long long* v_strides,
                     const long long* o_strides, const long long* do_strides, const long long* dq_strides,
                     const long long* dk_strides, const long long* dv_strides, int causal, float scale,
-                    const float* rope_cache, int rope_ctx, int flags, void* stream);
+                    const float* rope_cache, int rope_ctx, int flags, void* do_bf16_scratch, void* stream);
 
 /* ---- fused normalisation / elementwise ---------------------------------------------------------
  * ref: RMSNorm model.py:101-107, residual adds model.py:380-386. */
@@ -102,6 +122,10 @@ int b200_embedding_fwd(const long long* ids, const float* w, float* out, long lo
 int b200_embedding_bwd(const long long* ids, const float* dout, float* dw, long long T, int d, int vocab,
                        int zero_first, void* stream);
 int b200_cast_f32_to_bf16(const float* in, void* out, long long n, void* stream);
+/* Up to three contiguous fp32 -> bf16 casts in ONE launch (stop at the first n <= 0): the q, k, v operands of an fp32
+ * attention call.  ref: the implicit per-tensor casts of the Triton kernel's tl.dot operands (flash_attention.py:228). */
+int b200_cast3_f32_to_bf16(const float* in0, void* out0, long long n0, const float* in1, void* out1, long long n1,
+                           const float* in2, void* out2, long long n2, void* stream);
 
 /* ---- softmax cross-entropy -------------------------------------------------------------------
  * ref: cs336_basics/nn_utils.py:9-17. */
@@ -153,6 +177,18 @@ int b200_allreduce(const unsigned long long* peer_ptrs_host, const unsigned long
 int b200_bcast_pull(const unsigned long long* peer_ptrs_host, const unsigned long long* signal_ptrs_host,
                     long long byte_off, long long nbytes, int src_rank, int rank, int world_size, int blocks,
                     int signal_slot, void* stream);
+/* Broadcast by NVLS multicast store: rank src_rank writes nbytes at byte_off of its arena through the switch into
+ * every rank's arena (one multimem.st per 16 bytes; the source's NVLink egress is nbytes, not (ws-1)*nbytes).
+ * ref: dist.broadcast(param.data, src=0) per parameter at DDP construction (…sharded.py:225-226,260-261). */
+int b200_bcast_mc(const unsigned long long* peer_ptrs_host, const unsigned long long* signal_ptrs_host,
+                  void* multicast_ptr, long long byte_off, long long nbytes, int src_rank, int rank, int world_size,
+                  int blocks, int signal_slot, void* stream);
+/* Health of the NVLink kernels on the current device.  Their cross-rank barriers spin with a time limit
+ * (b200_comm_reset sets it, default 30 s); a barrier that runs out records (rank, CTA, peer, phase, slot, flag) and
+ * lets every later barrier fall through, so a lost rank shows up as status 1 here instead of a hung GPU.
+ * The reference has no counterpart (NCCL's watchdog plays this role for its collectives). */
+int b200_comm_status(int* info6 /*nullable*/);
+int b200_comm_reset(long long timeout_ms /*0: keep*/);
 /* Cross-rank barrier on the signal pads (orders peer stores before what follows on every rank). */
 int b200_symm_barrier(const unsigned long long* signal_ptrs_host, int rank, int world_size, int signal_slot,
                       void* stream);
@@ -172,6 +208,9 @@ int b200_adamw_multi_distribute(const b200_adamw_tensor* table_dev, const long l
  * arena, applies AdamW with its slice of m / v (optimizer state sharded 1/world_size), and stores the new fp32
  * parameters and bf16 shadows into every rank's parameter / shadow arenas (same element layout as the gradient
  * bucket; shadow offset = byte_off / 2).  m_slice / v_slice: ceil(ceil(numel/8)/ws)*8 floats, this rank only.
+ * defer_fp32 = 1: only the bf16 shadows cross NVLink here, plus the fp32 values of the n_eager (<= 4) element ranges
+ * [eager_lo, eager_hi) of the bucket that the next forward reads in fp32; the other fp32 replicas are brought up to
+ * date by b200_zero_param_gather (run it before anything reads them).
  * ref: all_reduce + grad/ws (…sharded.py:299,314) + optimizer.step + per-parameter broadcast (…:335-340). */
 int b200_zero_adamw_bucket(const unsigned long long* grad_peers_host, const unsigned long long* param_peers_host,
                            const unsigned long long* shadow_peers_host /*nullable*/,
@@ -179,7 +218,15 @@ int b200_zero_adamw_bucket(const unsigned long long* grad_peers_host, const unsi
                            const unsigned long long* multicast3_host /*nullable: NVLS addresses of grad, param, shadow arenas*/,
                            long long byte_off, long long numel, float* m_slice, float* v_slice, const float* hyper_dev,
                            const int* step_dev, int mode, int rank, int world_size, int blocks, int signal_slot,
-                           int variant /*bit0: NVLS reduce, bit1: NVLS stores*/, void* stream);
+                           int variant /*bit0: NVLS reduce, bit1: NVLS stores*/, int defer_fp32, int n_eager,
+                           const long long* eager_lo_elems, const long long* eager_hi_elems, void* stream);
+/* Deferred half of the above: every rank pushes its slice of the fp32 parameters of all n_buckets buckets
+ * (buckets_dev: device array of {byte_off, ceil(numel*4/32)} int64 pairs) into every other rank's parameter arena
+ * (peer stores, or multimem.st when param_multicast != 0), then one cross-rank barrier.
+ * ref: the per-parameter dist.broadcast loop (…sharded.py:337-340). */
+int b200_zero_param_gather(const unsigned long long* param_peers_host, const unsigned long long* signal_ptrs_host,
+                           unsigned long long param_multicast, const long long* buckets_dev, int n_buckets, int rank,
+                           int world_size, int blocks, int signal_slot, void* stream);
 int b200_incr_step(int* step_dev, void* stream);
 
 #ifdef __cplusplus

@@ -255,3 +255,60 @@ def test_clip_grad_norm():
     coef = min(1.0, 1.0 / (float(total) + 1e-6))
     for p, g in zip(ps, gs):
         torch.testing.assert_close(p.grad, g * coef, rtol=1e-4, atol=1e-6)
+
+
+# ------------------------------------------------------------------------------------------------ row softmax
+@pytest.mark.parametrize("rows,cols", [(1, 1), (5, 7), (33, 1000), (4, 10000), (2, 16384), (2, 20011)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_softmax_rows(rows, cols, dtype):
+    k = _k()
+    torch.manual_seed(0)
+    x = (torch.randn(rows, cols, device="cuda") * 3).to(dtype)
+    y = k.softmax_rows(x, out_dtype=torch.float32, scale=0.7)
+    ref = torch.softmax(x.float() * 0.7, -1)
+    torch.testing.assert_close(y, ref, rtol=2e-5, atol=1e-7)
+    torch.testing.assert_close(y.sum(-1), torch.ones(rows, device="cuda"), rtol=1e-5, atol=1e-5)
+    yb = k.softmax_rows(x, scale=0.7)  # same dtype out
+    assert yb.dtype == dtype and _rel_err(yb, ref) < (1e-6 if dtype == torch.float32 else 4e-3)
+
+
+def test_softmax_rows_causal_and_strided():
+    k = _k()
+    torch.manual_seed(1)
+    B, N = 3, 200
+    s = torch.randn(B * N, N + 8, device="cuda").bfloat16()[:, :N]  # row stride N + 8
+    p = k.softmax_rows(s, out_dtype=torch.float32, scale=0.125, causal_period=N)
+    mask = torch.ones(N, N, device="cuda", dtype=torch.bool).tril().repeat(B, 1)
+    ref = torch.softmax((s.float() * 0.125).masked_fill(~mask, float("-inf")), -1)
+    torch.testing.assert_close(p, ref, rtol=2e-5, atol=1e-7)
+    assert float(p[~mask].abs().max()) == 0.0
+
+
+def test_softmax_public_op_with_autograd():
+    from cs336_a2_systems_b200.ops import softmax
+    torch.manual_seed(2)
+    x = torch.randn(4, 6, 333, device="cuda", requires_grad=True)
+    w = torch.randn(4, 6, 333, device="cuda")
+    (softmax(x, -1) * w).sum().backward()
+    x2 = x.detach().clone().requires_grad_(True)
+    (torch.softmax(x2, -1) * w).sum().backward()
+    torch.testing.assert_close(x.grad, x2.grad, rtol=1e-4, atol=1e-6)
+    torch.testing.assert_close(softmax(x.detach(), 1), torch.softmax(x.detach(), 1))  # other dims: oracle path
+
+
+@pytest.mark.parametrize("N,D,causal,dtype", [(256, 64, True, torch.bfloat16), (200, 16, False, torch.bfloat16),
+                                               (384, 128, True, torch.float32)])
+def test_materialized_attention_matches_oracle(N, D, causal, dtype):
+    """The O(N^2)-memory comparison arm (GEMM + fused mask/softmax + GEMM, and its backward) against the oracle."""
+    from cs336_a2_systems_b200.ops import native
+    torch.manual_seed(3)
+    q, kk, v = (torch.randn(2, N, D, device="cuda").to(dtype).requires_grad_(True) for _ in range(3))
+    do = torch.randn(2, N, D, device="cuda").to(dtype)
+    o = native.materialized_attention(q, kk, v, causal)
+    o.backward(do)
+    q2, k2, v2 = (t.detach().float().requires_grad_(True) for t in (q, kk, v))
+    o_ref, _ = F_ref.attention_and_lse_ref(q2, k2, v2, causal)
+    o_ref.backward(do.float())
+    assert _rel_err(o, o_ref) < 1.5e-2
+    for a, b in ((q, q2), (kk, k2), (v, v2)):
+        assert _rel_err(a.grad, b.grad) < 3e-2

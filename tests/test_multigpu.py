@@ -137,3 +137,146 @@ def _ddp_worker(rank, ws, port):
 def test_ddp_symm_backends_match_c10d():
     ws = min(torch.cuda.device_count(), 8)
     mp.spawn(_ddp_worker, args=(ws, find_free_port()), nprocs=ws, join=True)
+
+
+def _zero_variants_worker(rank, ws, port):
+    """Every variant of the bucket-fused ZeRO-1 kernel (P2P / NVLS reduce / NVLS stores / both) with and without the
+    deferred fp32 gather must land on the parameters of plain NVLink DDP + replicated AdamW, with identical replicas
+    on every rank after ``sync_params()``; eager and CUDA-graph trainers."""
+    import copy
+    import torch.distributed as dist
+    from cs336_a2_systems_b200.models import TransformerLM
+    from cs336_a2_systems_b200.ops import kernels
+    from cs336_a2_systems_b200.optim import AdamW
+    from cs336_a2_systems_b200.parallel import DDPBucketed, ShardedOptimizer
+    from cs336_a2_systems_b200.train import Trainer
+    dev = _init(rank, ws, port)
+    kernels.comm_reset(20000)
+    torch.manual_seed(0)
+    base = TransformerLM(vocab_size=512, context_length=128, d_model=128, num_layers=3, num_heads=2, d_ff=256).to(dev)
+    g = torch.Generator().manual_seed(11 + rank)
+    batches = [torch.randint(0, 512, (2, 128), generator=g).to(dev) for _ in range(12)]
+
+    def run(make_opt, graph, steps):
+        m = DDPBucketed(copy.deepcopy(base), 0.25, backend="symm")
+        opt = make_opt(m)
+        tr = Trainer(m, opt, autocast=True, cuda_graph=graph)
+        losses = [float(tr.step(x, torch.roll(x, -1, 1))) for x in batches[:steps]]
+        if hasattr(opt, "sync_params"):
+            opt.sync_params()
+        torch.cuda.synchronize()
+        kernels.comm_check()
+        return m, losses
+
+    ref, ref_losses = run(lambda m: AdamW(m.parameters(), lr=1e-3, weight_decay=0.1), False, 8)
+    refp = dict(ref.module.named_parameters())
+    have_mc = bool(ref._reducer.arena.multicast_ptr)
+    for variant in ([0, 1, 2, 3] if have_mc else [0]):
+        for defer in (False, True):
+            for graph in (False, True):
+                def make(m, variant=variant, defer=defer):
+                    o = ShardedOptimizer(m.parameters(), AdamW, lr=1e-3, weight_decay=0.1)
+                    assert o.enable_symmetric(m, defer_fp32_gather=defer, variant=variant)
+                    assert o._symm.variant == variant and o._symm.defer == defer
+                    return o
+                m, losses = run(make, graph, 8)
+                tag = f"variant {variant} defer {defer} graph {graph}"
+                assert abs(losses[-1] - ref_losses[-1]) < 5e-2, f"{tag}: losses {losses} vs {ref_losses}"
+                for n, p in m.module.named_parameters():
+                    d = (p - refp[n]).abs()
+                    bad = d > 2e-4 + 2e-3 * refp[n].abs()
+                    assert bad.float().mean().item() < 2e-3 and d.max().item() < 1e-2, f"{tag} {n}: {d.max().item():.3e}"
+                    gathered = [torch.empty_like(p) for _ in range(ws)]
+                    dist.all_gather(gathered, p.detach().contiguous())
+                    assert all(torch.equal(t, gathered[0]) for t in gathered), f"{tag} {n} differs across ranks"
+                del m
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_zero_kernel_variants_match_replicated_adamw():
+    ws = min(torch.cuda.device_count(), 8)
+    mp.spawn(_zero_variants_worker, args=(ws, find_free_port()), nprocs=ws, join=True)
+
+
+def _bcast_and_watchdog_worker(rank, ws, port):
+    import torch.distributed as dist
+    from cs336_a2_systems_b200.ops import kernels
+    from cs336_a2_systems_b200.parallel import symm
+    dev = _init(rank, ws, port)
+    # multicast-store broadcast vs pull broadcast: both must deliver the source's bytes everywhere
+    n = (1 << 20) + 40
+    arena = symm.SymmArena(n * 4 + 256, dev, None)
+    for src in range(min(ws, 2)):
+        for how in (["mc", "pull"] if arena.multicast_ptr else ["pull"]):
+            buf = arena.view(0, n, torch.float32)
+            torch.manual_seed(rank * 7 + src)
+            buf.normal_()
+            want = buf.clone()
+            dist.broadcast(want, src=src)
+            torch.cuda.synchronize()
+            dist.barrier()
+            (kernels.bcast_mc if how == "mc" else kernels.bcast_pull)(arena, 0, n * 4, src)
+            torch.cuda.synchronize()
+            assert torch.equal(buf, want), f"bcast {how} src {src}"
+    # bounded barrier: a rank that never shows up turns into a status record, not a hung GPU
+    dist.barrier()
+    scratch = symm.SymmArena(4096, dev, None)
+    kernels.comm_reset(300)
+    assert kernels.comm_status() is None
+    if rank == 0:
+        kernels.symm_barrier(scratch, 0)  # nobody answers
+        torch.cuda.synchronize()
+        st = kernels.comm_status()
+        assert st is not None and st[0] == 0 and st[3] in (1, 2), st
+        with pytest.raises(RuntimeError, match="communicator dead"):
+            kernels.comm_check()
+    dist.barrier()
+    kernels.comm_reset(30000)
+    assert kernels.comm_status() is None
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_multicast_broadcast_and_barrier_time_limit():
+    ws = min(torch.cuda.device_count(), 8)
+    mp.spawn(_bcast_and_watchdog_worker, args=(ws, find_free_port()), nprocs=ws, join=True)
+
+
+def _zero_long_graph_worker(rank, ws, port):
+    """50 CUDA-graph replays of the bucket-fused step with the default variant for this world size and the deferred
+    gather: must finish (bounded barriers report instead of hanging), keep replicas identical and reduce the loss."""
+    import torch.distributed as dist
+    from cs336_a2_systems_b200.models import TransformerLM
+    from cs336_a2_systems_b200.ops import kernels
+    from cs336_a2_systems_b200.optim import AdamW
+    from cs336_a2_systems_b200.parallel import DDPBucketed, ShardedOptimizer
+    from cs336_a2_systems_b200.train import Trainer
+    dev = _init(rank, ws, port)
+    kernels.comm_reset(20000)
+    torch.manual_seed(0)
+    model = TransformerLM(vocab_size=1000, context_length=256, d_model=256, num_layers=4, num_heads=4, d_ff=1024).to(dev)
+    m = DDPBucketed(model, 1.0, backend="symm")
+    opt = ShardedOptimizer(m.parameters(), AdamW, lr=1e-3, weight_decay=0.01)
+    assert opt.enable_symmetric(m, defer_fp32_gather=True)
+    tr = Trainer(m, opt, autocast=True, cuda_graph=True)
+    g = torch.Generator().manual_seed(3 + rank)
+    x = torch.randint(0, 1000, (4, 256), generator=g).to(dev)
+    y = torch.roll(x, -1, 1)
+    losses = [float(tr.step(x, y)) for _ in range(54)]
+    assert tr._graph is not None
+    opt.sync_params()
+    torch.cuda.synchronize()
+    kernels.comm_check()
+    assert losses[-1] < losses[0] - 0.5, losses[::6]
+    for n, p in m.module.named_parameters():
+        gathered = [torch.empty_like(p) for _ in range(ws)]
+        dist.all_gather(gathered, p.detach().contiguous())
+        assert all(torch.equal(t, gathered[0]) for t in gathered), f"{n} differs across ranks"
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_zero_fused_step_50_graph_replays():
+    ws = min(torch.cuda.device_count(), 8)
+    mp.spawn(_zero_long_graph_worker, args=(ws, find_free_port()), nprocs=ws, join=True)

@@ -1,11 +1,11 @@
-"""Hardware check of the opt-in FlashAttention kernel variants against a materialised fp32 oracle, plus timings on
-the 16x16384x64 causal shape.  The variants are selected by environment variables that the library reads once per
-process, so set them on the command line:
+"""Hardware check of the FlashAttention kernels against a materialised fp32 oracle on awkward shapes (ragged tails,
+head dims 16 / 80 / 128, causal or not), plus timings on the leaderboard shape (16 x 16384 x 64 causal), the LM shape
+(100 x 512 x 64) and a head-dim-128 shape, each with the 2-CTA cluster launch (K/V multicast) and the plain launch.
 
-    python tools/fa_variants_check.py                                  # default kernels
-    B200SYS_FA_FWD_WG2=1 python tools/fa_variants_check.py             # forward, two softmax warpgroups (2: + O in TMEM)
-    B200SYS_FA_BWD_WG=2 python tools/fa_variants_check.py              # backward, 2 (or 4) softmax column groups
+    python tools/fa_check.py [--json out.json]
 """
+import argparse
+import json
 import os
 import sys
 
@@ -13,8 +13,11 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch  # noqa: E402
 
 from cs336_a2_systems_b200.ops import kernels as k  # noqa: E402
+from cs336_a2_systems_b200.utils.clocks import ClockSampler  # noqa: E402
 
-print("variants:", {v: os.environ.get(v, "-") for v in ("B200SYS_FA_FWD_WG2", "B200SYS_FA_BWD_WG")}, flush=True)
+ap = argparse.ArgumentParser()
+ap.add_argument("--json", default=None)
+args = ap.parse_args()
 torch.manual_seed(0)
 ok = True
 for (B, H, N, D, causal) in [(2, 3, 512, 64, True), (1, 2, 1000, 64, False), (1, 2, 384, 128, True), (1, 1, 300, 16, True),
@@ -35,10 +38,11 @@ for (B, H, N, D, causal) in [(2, 3, 512, 64, True), (1, 2, 1000, 64, False), (1,
     ok &= errs["O"] < 3e-2 and errs["L"] < 2e-3 and max(errs["dQ"], errs["dK"], errs["dV"]) < 2e-2
 
 
-def timed(fn, n=10):
+def timed(fn, n=20):
     for _ in range(3):
         fn()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
     e0.record()
     for _ in range(n):
         fn()
@@ -47,9 +51,21 @@ def timed(fn, n=10):
     return e0.elapsed_time(e1) / n
 
 
-for (B, H, N, D) in [(1, 16, 16384, 64), (100, 1, 512, 64), (1, 8, 16384, 128)]:
+rows = []
+for (B, H, N, D) in [(1, 16, 16384, 64), (100, 1, 512, 64), (4, 25, 512, 64), (1, 8, 16384, 128), (1, 32, 4096, 80)]:
     q, kk, v, do = (torch.randn(B, H, N, D, device="cuda").bfloat16() for _ in range(4))
     o, lse = k.fa2_fwd(q, kk, v, True)
-    print(f"{B}x{H}x{N}x{D} causal: fwd {timed(lambda: k.fa2_fwd(q, kk, v, True)):.3f} ms, "
-          f"bwd {timed(lambda: k.fa2_bwd(q, kk, v, o, lse, do, True)):.3f} ms", flush=True)
+    with ClockSampler(0, period_ms=50) as clk:
+        f1 = timed(lambda: k.fa2_fwd(q, kk, v, True, cluster=True))
+        f0 = timed(lambda: k.fa2_fwd(q, kk, v, True, cluster=False))
+        bw = timed(lambda: k.fa2_bwd(q, kk, v, o, lse, do, True))
+    fl = 4.0 * B * H * N * N * D * 0.5
+    row = dict(B=B, H=H, N=N, D=D, causal=True, fwd_cluster_ms=f1, fwd_plain_ms=f0, bwd_ms=bw,
+               fwd_tflops=fl / min(f0, f1) / 1e9, bwd_tflops=2.5 * fl / bw / 1e9, clocks=clk.summary())
+    rows.append(row)
+    print(f"{B}x{H}x{N}x{D} causal: fwd cluster {f1:.3f} ms / plain {f0:.3f} ms ({row['fwd_tflops']:.0f} TF/s), "
+          f"bwd {bw:.3f} ms ({row['bwd_tflops']:.0f} TF/s) clocks {row['clocks'].get('sm_mhz')} MHz "
+          f"{row['clocks'].get('reasons')}", flush=True)
+if args.json:
+    json.dump(rows, open(args.json, "w"), indent=1)
 print("PARITY_OK" if ok else "PARITY_FAIL")
