@@ -53,12 +53,14 @@ def parse_args():
     ap.add_argument("--defer-gather", choices=["auto", "0", "1"], default="auto",
                     help="ours, sharded: refresh the fp32 replicas of Linear weights under the NEXT forward instead "
                          "of inside the backward-overlapped bucket kernels (bf16 GEMM shadows and fp32-read "
-                         "parameters are always distributed at once); 'auto' = on from 4 ranks up")
+                         "parameters are always distributed at once); 'auto' = off (measured slower at 2 and 8 GPUs)")
     ap.add_argument("--zero-variant", type=int, default=None,
                     help="ours, sharded: bucket kernel variant (bit 0 NVLS reduce, bit 1 NVLS stores); default by N")
     ap.add_argument("--watchdog-s", type=float, default=420.0,
                     help="abort the whole process (exit code 3, one JSON error line) if the run has not finished "
                          "after this many seconds, instead of sitting in a collective until its 10-minute timeout")
+    ap.add_argument("--no-opt-in-bwd", action="store_true",
+                    help="ours, 1 GPU: keep AdamW a separate pass after backward instead of the wgrad GEMM epilogues")
     ap.add_argument("--no-overlap", action="store_true",
                     help="ours: run the optimizer after backward instead of overlapping it with backward")
     return ap.parse_args()
@@ -136,7 +138,8 @@ def build_ours(args, rank, ws, dev):
     symm_backend = getattr(getattr(model, "_reducer", None), "kind", "") == "symm"
     explicit = args.sharded or args.optimizer == "sharded"
     shard = ws > 1 and (explicit or (args.optimizer == "auto" and symm_backend))
-    defer = (ws >= 4) if args.defer_gather == "auto" else args.defer_gather == "1"
+    # measured at 2 and 8 GPUs (profiles/r2): deferring costs more than it hides, so 'auto' keeps it off
+    defer = args.defer_gather == "1"
     opt = None
     if shard:
         from cs336_a2_systems_b200.parallel import ShardedOptimizer
@@ -166,7 +169,7 @@ def build_ours(args, rank, ws, dev):
     trainer = Trainer(model, opt, autocast=True,
                       cuda_graph=not args.no_graph and (bucket_fused or not args.shard_effective),
                       overlap_optimizer=not args.no_overlap and not args.shard_effective,
-                      graph_warmup_steps=2)
+                      graph_warmup_steps=2, optimizer_in_backward=False if args.no_opt_in_bwd else None)
     state = {"launches_per_step": 0, "trainer": trainer, "optimizer": opt}
 
     def step_device(x, y):
@@ -184,6 +187,7 @@ def build_ours(args, rank, ws, dev):
     extra = {"cuda_graph": trainer.cuda_graph, "optimizer_overlapped_with_backward": trainer._overlap is not None,
              "sharded_optimizer": args.shard_effective, "fused_nvlink_sharded_adamw": fused_sharded,
              "bucket_fused_reduce_scatter_adamw_allgather": bucket_fused,
+             "optimizer_in_wgrad_epilogue": trainer.optimizer_in_backward,
              "zero_kernel_variant": getattr(sym, "variant", None) if bucket_fused else None,
              "deferred_fp32_param_gather": bool(getattr(sym, "defer", False)) if bucket_fused else None,
              "comm": getattr(getattr(model, "_reducer", None), "kind", "none")}
@@ -324,12 +328,15 @@ def _main(args):
     final_loss = last.get("loss")
     loss_at[n_warm + 2 * args.steps] = final_loss
     peak = torch.cuda.max_memory_allocated() / 2 ** 30
+    free_b, total_b = torch.cuda.mem_get_info()
+    used_dev = (total_b - free_b) / 2 ** 30  # driver view: also counts NVLink symmetric arenas and the allocator's cache
     peaks = [peak]
     if ws > 1:
-        t = torch.tensor([peak], dtype=torch.float64, device=dev)
+        t = torch.tensor([peak, used_dev], dtype=torch.float64, device=dev)
         allp = [torch.zeros_like(t) for _ in range(ws)]
         dist.all_gather(allp, t)
-        peaks = [float(a.item()) for a in allp]
+        peaks = [float(a[0].item()) for a in allp]
+        used_dev = max(float(a[1].item()) for a in allp)
     if rank == 0:
         from cs336_a2_systems_b200.models import get_model_config
         cfg = get_model_config(args.model)
@@ -339,6 +346,8 @@ def _main(args):
             placement = "AdamW state sharded 1/N (ZeRO-1), update fused into the per-bucket NVLink reduce kernel"
         elif extra.get("sharded_optimizer"):
             placement = "AdamW state sharded by parameter owner"
+        elif extra.get("optimizer_in_wgrad_epilogue"):
+            placement = "AdamW applied inside the wgrad GEMM epilogues"
         else:
             placement = "AdamW replicated"
         out = {
@@ -364,6 +373,9 @@ def _main(args):
             "loss_at_step": {str(k): v for k, v in loss_at.items()},
             "loss_first": loss_at.get(1), "loss_last": final_loss,
             "peak_mem_gib": round(max(peaks), 2), "peak_mem_gib_per_rank": [round(x, 2) for x in peaks],
+            # torch's allocator does not see the NVLink symmetric arenas (gradients / parameters / shadows of the fused
+            # ZeRO path): the driver-level figure at the end of the run is the honest memory footprint per GPU
+            "device_mem_used_gib_max": round(used_dev, 2),
         }
         if comm_dead is not None:
             out["error"] = "NVLink communicator reported a timed-out barrier (rank, cta, peer, phase, slot, flag) = %s" % (comm_dead,)

@@ -20,7 +20,7 @@ from .._native import check, p, stream_ptr
 BF16, F32 = 0, 1
 _DT = {torch.bfloat16: BF16, torch.float32: F32}
 
-EPI_BF16, EPI_F32, EPI_F32_ACC, EPI_BF16_SWIGLU, EPI_F32_RESID, EPI_BF16_ROPE, EPI_F32_T = 0, 1, 2, 3, 4, 5, 6
+EPI_BF16, EPI_F32, EPI_F32_ACC, EPI_BF16_SWIGLU, EPI_F32_RESID, EPI_BF16_ROPE, EPI_F32_T, EPI_ADAMW = 0, 1, 2, 3, 4, 5, 6, 7
 
 #: route eligible GEMMs through the CTA-pair (cta_group::2) kernel
 GEMM_PAIR = _environ.get("B200SYS_GEMM_PAIR", "auto")  # "auto": per-shape choice, "1": always when legal, "0": never
@@ -395,6 +395,70 @@ class AdamWLaunch:
               "adamw_multi")
         _count(2)
         bump_param_epoch()
+
+
+class DeviceHyper:
+    """AdamW hyper-parameters (lr, beta1, beta2, eps, weight_decay, grad_scale) and the step counter ``t`` in device
+    memory, for kernels that must stay valid inside a CUDA graph: values change through a pinned staging ring and an
+    async copy, never through a kernel argument."""
+
+    def __init__(self, device, step0: int = 1):
+        self.hyper = torch.zeros(8, dtype=torch.float32, device=device)
+        self._host = torch.zeros(16, 8, dtype=torch.float32).pin_memory()
+        self._slot = 0
+        self._vals = None
+        self.step = torch.tensor([step0], dtype=torch.int32, device=device)
+
+    def set(self, lr, b1, b2, eps, wd, grad_scale=1.0) -> None:
+        vals = (float(lr), float(b1), float(b2), float(eps), float(wd), float(grad_scale))
+        if vals == self._vals or torch.cuda.is_current_stream_capturing():
+            return  # (a copy recorded into a graph would replay stale staging contents: see AdamWLaunch.set_hyper)
+        self._vals = vals
+        row = self._host[self._slot]
+        self._slot = (self._slot + 1) % self._host.shape[0]
+        row[:6] = torch.tensor(vals, dtype=torch.float32)
+        self.hyper.copy_(row, non_blocking=True)
+
+    def advance(self) -> None:
+        check(_lib().b200_incr_step(p(self.step), stream_ptr()), "incr_step")
+        _count()
+
+
+class _WgradAdamwArgs(ctypes.Structure):
+    _fields_ = [("p", c_void_p * 3), ("m", c_void_p * 3), ("v", c_void_p * 3), ("rows", c_int * 3), ("nseg", c_int),
+                ("mode", c_int), ("shadow", c_void_p), ("hyper", c_void_p), ("step", c_void_p)]
+
+
+def wgrad_adamw(dy: Tensor, x: Tensor, params, ms, vs, shadow: Tensor | None, dh: DeviceHyper, mode: int = 0,
+                grad_out: Tensor | None = None, pair: bool | None = None) -> None:
+    """``dW = dyᵀ·x`` consumed by AdamW inside the GEMM epilogue (``EPI_ADAMW``): ``params`` (1..3 contiguous fp32
+    ``[rows_i, N]`` tensors stacked along the rows of dW, in the order of their fused forward GEMM) and their moments
+    are updated in place, ``shadow`` (bf16 ``[Σrows, N]``) is rewritten; the gradient is only stored when ``grad_out``
+    (fp32 ``[Σrows, N]``) is given."""
+    T, M = dy.shape
+    N = x.shape[1]
+    assert x.shape[0] == T and dy.dtype == x.dtype == torch.bfloat16 and dy.stride(1) == 1 and x.stride(1) == 1
+    assert 1 <= len(params) <= 3 and sum(q.shape[0] for q in params) == M
+    a = _WgradAdamwArgs()
+    for i, (q, m_, v_) in enumerate(zip(params, ms, vs)):
+        assert q.dtype == torch.float32 and q.is_contiguous() and q.shape[1] == N
+        assert m_.is_contiguous() and v_.is_contiguous() and m_.shape == q.shape == v_.shape
+        a.p[i], a.m[i], a.v[i], a.rows[i] = q.data_ptr(), m_.data_ptr(), v_.data_ptr(), q.shape[0]
+    a.nseg, a.mode = len(params), mode
+    if shadow is not None:
+        assert shadow.dtype == torch.bfloat16 and shadow.is_contiguous() and tuple(shadow.shape) == (M, N)
+        a.shadow = shadow.data_ptr()
+    a.hyper, a.step = dh.hyper.data_ptr(), dh.step.data_ptr()
+    if grad_out is not None:
+        assert grad_out.dtype == torch.float32 and grad_out.is_contiguous() and tuple(grad_out.shape) == (M, N)
+    if pair is None:
+        use_pair, bn = _plan_gemm(M, N, True, M >= 256) if GEMM_PAIR == "auto" else (GEMM_PAIR == "1" and M >= 256, 0)
+    else:
+        use_pair, bn = pair, 0
+    check(_lib().b200_wgrad_adamw(p(dy), p(x), c_int(T), c_int(M), c_int(N), c_int(dy.stride(0)), c_int(x.stride(0)),
+                                  ctypes.byref(a), p(grad_out), c_int(int(use_pair)), c_int(bn), stream_ptr()),
+          "wgrad_adamw")
+    _count()
 
 
 _clip_plans: dict = {}

@@ -154,6 +154,14 @@ class LinearFn(torch.autograd.Function):
                 dx = dx.to(ctx.x_dtype)
         ws = ctx.weights
         need = ctx.needs_input_grad[3:]
+        # optimizer in the wgrad epilogue (AdamW.fuse_into_backward): the whole group must belong to one fused group,
+        # each weight mirrored by exactly this shadow, nothing accumulated into .grad yet
+        grp = getattr(ws[0], "_b200_bwd_opt", None)
+        if grp is not None and all(need) and all(getattr(w, "_b200_bwd_opt", None) is grp and w.grad is None and
+                                                 len(getattr(w, "_b200_shadow_slices", ())) == 1 for w in ws) and \
+                wb.is_contiguous() and torch.is_grad_enabled() is False:
+            grp.wgrad(dy2, x2, ws, wb)
+            return (dx, None, None, *([None] * len(ws)))
         if len(ws) > 1 and all(need):
             joint = grad_slots.claim_group(ws)
             if joint is not None:

@@ -49,6 +49,7 @@ class AdamW(torch.optim.Optimizer):
         self._fused = fused
         self._plans: dict[object, object] = {}
         self._done: set[int] = set()  # ids of params already stepped this iteration by step_subset()
+        self._bwd_groups: dict[int, "_BackwardFusedGroup"] = {}  # see fuse_into_backward()
 
     # ------------------------------------------------------------------ reference arithmetic
     @staticmethod
@@ -99,8 +100,43 @@ class AdamW(torch.optim.Optimizer):
                     self._step_param_torch(p, self.state[p], lr, b1, b2, eps, wd)
             if fused_ps:
                 self._step_fused(gi, fused_ps, lr, b1, b2, eps, wd)
+        for grp in self._bwd_groups.values():
+            grp.finish_step()
         self._done.clear()
         return loss
+
+    # ------------------------------------------------------------------ optimizer inside the wgrad GEMM epilogue
+    def fuse_into_backward(self, module: torch.nn.Module | None = None, enable: bool = True) -> int:
+        """Let the weight-gradient GEMMs of the native ``Linear`` layers apply this optimizer in their epilogue
+        (``csrc/gemm_epilogue.cuh: EPI_ADAMW``): the fp32 dW tile in the accumulator is combined with p, m, v of the
+        same elements and p, m, v and the bf16 GEMM shadow are written back — the gradient of those weights never
+        reaches HBM (no 4 B/param write in the GEMM, no 4 B/param read in the optimizer) and their update overlaps
+        the tensor-core work of backward.  ``step()`` then only advances the step counter for them (and updates
+        everything else: norm gains, embeddings, …).
+
+        Same arithmetic and state (``m``, ``v``, ``t``) as ``step()``.  Restrictions: ``param.grad`` stays ``None``
+        for fused weights (so no gradient clipping / accumulation / inspection — the caller must not need them),
+        every fused weight must take part in every backward, and hyper-parameters are read at backward time.
+        Returns the number of parameters registered; ``enable=False`` undoes it."""
+        from ..models.layers import Linear
+
+        for grp in self._bwd_groups.values():
+            grp.release()
+        self._bwd_groups = {}
+        if not enable or self._fused is False or _native.force_torch():
+            return 0
+        wanted = None
+        if module is not None:
+            wanted = {id(m.weight) for m in module.modules() if isinstance(m, Linear)}
+        n = 0
+        for gi, g in enumerate(self.param_groups):
+            ps = [p for p in g["params"] if p.is_cuda and p.dtype == torch.float32 and p.dim() == 2 and
+                  p.is_contiguous() and p.requires_grad and (wanted is None or id(p) in wanted)]
+            if ps:
+                self._bwd_groups[gi] = _BackwardFusedGroup(self, gi, ps)
+                n += len(ps)
+        return n
+
 
     @torch.no_grad()
     def step_subset(self, key, params, max_blocks: int = 0) -> None:
@@ -166,6 +202,8 @@ class AdamW(torch.optim.Optimizer):
         super().load_state_dict(state_dict)
         self._plans.clear()
         self._done.clear()
+        for grp in self._bwd_groups.values():
+            grp.reload_state()
 
     def __setstate__(self, state) -> None:
         super().__setstate__(state)
@@ -182,6 +220,8 @@ class AdamW(torch.optim.Optimizer):
             g = self.param_groups[k if isinstance(k, int) else k[0]]
             b1, b2 = g["betas"]
             plan.set_hyper(g["lr"], b1, b2, g["eps"], g["weight_decay"])
+        for grp in self._bwd_groups.values():
+            grp.push_hyper()
 
     def sync_step_from_device(self) -> None:
         """After CUDA-graph replays the host ``t`` mirrors are stale; refresh them from the device."""
@@ -190,3 +230,75 @@ class AdamW(torch.optim.Optimizer):
             for p in plan.params:
                 self.state[p]["t"] = t
             plan.host_step = t
+        for grp in self._bwd_groups.values():
+            grp.sync_from_device()
+
+
+class _BackwardFusedGroup:
+    """The weights of one param group whose AdamW update runs inside their wgrad GEMM (``AdamW.fuse_into_backward``).
+    Holds the device-resident hyper-parameters / step counter the epilogues read, and marks every weight with a
+    back-pointer (``_b200_bwd_opt``) that ``ops.native.LinearFn.backward`` looks for."""
+
+    def __init__(self, opt: AdamW, gi: int, params):
+        from ..ops import kernels
+
+        self.opt, self.gi, self.params = opt, gi, list(params)
+        t0 = None
+        for p in self.params:
+            st = opt.state[p]
+            if "m" not in st:
+                st["m"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+                st["v"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+                st["t"] = 1
+            t0 = st["t"] if t0 is None else t0
+            if st["t"] != t0:
+                raise ValueError("fuse_into_backward: the weights of a param group must share one step count")
+            p._b200_bwd_opt = self
+        self.dh = kernels.DeviceHyper(self.params[0].device, step0=t0 or 1)
+        self.touched = False
+        self.push_hyper()
+
+    def release(self) -> None:
+        for p in self.params:
+            if getattr(p, "_b200_bwd_opt", None) is self:
+                del p._b200_bwd_opt
+
+    def push_hyper(self) -> None:
+        g = self.opt.param_groups[self.gi]
+        b1, b2 = g["betas"]
+        self.dh.set(g["lr"], b1, b2, g["eps"], g["weight_decay"])
+
+    def wgrad(self, dy2, x2, weights, shadow, grad_out=None) -> None:
+        """Called from ``LinearFn.backward`` in place of the plain wgrad GEMM."""
+        from ..ops import kernels
+
+        if not self.touched:  # first weight of this backward: hyper-parameters as they are NOW
+            self.push_hyper()
+            self.touched = True
+        st = self.opt.state
+        kernels.wgrad_adamw(dy2, x2, [w.data for w in weights], [st[w]["m"] for w in weights],
+                            [st[w]["v"] for w in weights], shadow, self.dh, mode=0, grad_out=grad_out)
+
+    def finish_step(self) -> None:
+        from ..ops import kernels
+
+        if not self.touched:
+            return
+        self.dh.advance()
+        for p in self.params:
+            self.opt.state[p]["t"] += 1
+        self.touched = False
+        kernels.bump_param_epoch()
+
+    def reload_state(self) -> None:
+        """After ``load_state_dict``: the moments are new tensors (looked up per launch, nothing cached) and the device
+        step counter must equal the restored ``t``."""
+        t = self.opt.state[self.params[0]].get("t", 1)
+        self.dh.step.fill_(int(t))
+        for p in self.params:
+            p._b200_bwd_opt = self
+
+    def sync_from_device(self) -> None:
+        t = int(self.dh.step.item())
+        for p in self.params:
+            self.opt.state[p]["t"] = t

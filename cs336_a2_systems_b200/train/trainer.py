@@ -113,7 +113,8 @@ class _OptimizerOverlap:
 class Trainer:
     def __init__(self, model: torch.nn.Module, optimizer: torch.optim.Optimizer, *, autocast: bool = True,
                  max_grad_norm: float | None = None, cuda_graph: bool = False, grad_arena: bool | None = None,
-                 overlap_optimizer: bool = False, overlap_unit_mb: float = 128.0, graph_warmup_steps: int = 3):
+                 overlap_optimizer: bool = False, overlap_unit_mb: float = 128.0, graph_warmup_steps: int = 3,
+                 optimizer_in_backward: bool | None = None):
         self.model = model
         self.optimizer = optimizer
         self.autocast = autocast
@@ -129,11 +130,28 @@ class Trainer:
         if max_grad_norm is not None and hasattr(getattr(optimizer, "_symm", None), "_reduce_bucket"):
             raise ValueError("the bucket-fused sharded AdamW applies the update as each bucket's gradients arrive; "
                              "it cannot be combined with global gradient-norm clipping")
+        # Single-process CUDA training with this package's AdamW and no clipping: run the optimizer of the Linear weights
+        # inside their wgrad GEMM epilogues (their gradients never reach HBM); everything else still goes through step()
+        self.optimizer_in_backward = False
+        want = optimizer_in_backward
+        if want is None:
+            want = os.environ.get("B200SYS_OPT_IN_BWD", "1") == "1"
+        if want and self.device.type == "cuda" and not self._is_ddp and max_grad_norm is None and \
+                hasattr(optimizer, "fuse_into_backward") and autocast:
+            self.optimizer_in_backward = optimizer.fuse_into_backward(model) > 0
+        elif optimizer_in_backward:
+            raise ValueError("optimizer_in_backward needs single-process CUDA training under autocast with "
+                             "cs336_a2_systems_b200.optim.AdamW and no gradient clipping")
+        if self.optimizer_in_backward:
+            overlap_optimizer = False  # what is left for step() (norm gains, embeddings) is a few microseconds
         self.arena = None
         if grad_arena or (grad_arena is None and self.device.type == "cuda" and not self._is_ddp):
             # opt-in (not yet timed on hardware): lay w3's slot next to w1's so their wgrads become ONE GEMM
             fuse_w13 = os.environ.get("B200SYS_FUSE_W13_WGRAD", "1") == "1"
-            self.arena = GradArena(grad_slots.fusion_friendly_order(model) if fuse_w13 else list(model.parameters()))
+            order = grad_slots.fusion_friendly_order(model) if fuse_w13 else list(model.parameters())
+            # weights updated inside their wgrad GEMM never materialise a gradient: no slot (and no memory) for them
+            order = [p for p in order if getattr(p, "_b200_bwd_opt", None) is None]
+            self.arena = GradArena(order) if any(p.requires_grad for p in order) else None
         self._overlap = None
         if overlap_optimizer and self.device.type == "cuda" and max_grad_norm is None and \
                 hasattr(optimizer, "step_subset"):

@@ -378,8 +378,8 @@ extern "C" int b200_bcast_mc(const unsigned long long* peer_ptrs_host, const uns
   if (nbytes <= 0) return 0;
   Peers P;
   if (int rc = load_peers(peer_ptrs_host, signal_ptrs_host, world_size, &P)) return rc;
-  if (blocks <= 0) blocks = 48;
-  if (blocks > kMaxBlocks) blocks = kMaxBlocks;
+  // only the source moves data and nothing else runs at DDP construction: one CTA per SM keeps the switch fed
+  if (blocks <= 0 || blocks > kSignalBlocks) blocks = kSignalBlocks;
   bcast_mc_kernel<<<blocks, kThreads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       P, static_cast<char*>(multicast_ptr), byte_off, (nbytes + 15) / 16, src_rank, rank, world_size, signal_slot);
   B200_LAUNCH_CHECK();

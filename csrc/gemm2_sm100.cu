@@ -154,6 +154,8 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const int ew = warp - 4;
     int acc = 0;
     uint32_t acc_phase = 0;
+    AdamwConsts ak;
+    if constexpr (EPI == EPI_ADAMW) ak = adamw_consts(p.opt);
     for (int t = cluster_id; t < total_tiles; t += num_clusters) {
       const int m0 = ((t % num_m2) * 2 + (int)cta_rank) * BM;
       const int n0 = (t / num_m2) * BN;
@@ -167,7 +169,8 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         uint32_t r[32];
         ptx::tmem_ld_32x32b_x32(t_row + c * 32, r);
         ptx::tmem_ld_wait();
-        store_chunk<EPI>(p, row, n0 + c * 32, r);
+        if constexpr (EPI == EPI_ADAMW) adamw_chunk(p, ak, row, n0 + c * 32, r);
+        else store_chunk<EPI>(p, row, n0 + c * 32, r);
       }
       ptx::tc_fence_before();
       __syncwarp();
@@ -229,6 +232,9 @@ static int dispatch_epi2(int epi, const CUtensorMap& a, const CUtensorMap& b, co
     case EPI_BF16_ROPE:
       if constexpr (!A_MN && !B_MN) return launch2<BN, A_MN, B_MN, EPI_BF16_ROPE>(a, b, p, s);
       break;
+    case EPI_ADAMW:
+      if constexpr (A_MN && B_MN) return launch2<BN, A_MN, B_MN, EPI_ADAMW>(a, b, p, s);
+      break;
   }
   set_error("gemm2: epilogue %d not available in the CTA-pair kernel for this layout", epi);
   return B200_ERR_UNSUPPORTED;
@@ -252,6 +258,41 @@ static int dispatch_major2(bool a_mn, bool b_mn, int epi, const CUtensorMap& a, 
 extern "C" int b200_gemm2_bf16_ex(const void* A, const void* B, void* C, const void* aux, int M, int N, int K, int lda,
                                   int ldb, int ldc, int ld_aux, int a_mn_major, int b_mn_major, int epilogue,
                                   int force_bn, int rope_S, int rope_dh, int rope_cols, int rope_ctx, void* stream) {
+  return b200::gemm::gemm2_run(A, B, C, aux, M, N, K, lda, ldb, ldc, ld_aux, a_mn_major, b_mn_major, epilogue, force_bn,
+                               rope_S, rope_dh, rope_cols, rope_ctx, nullptr, stream);
+}
+
+// Weight-gradient GEMM with the optimizer in its epilogue: dW[M, N] = dyᵀ·x (dy: [T, M], x: [T, N], bf16 row-major) is
+// never stored — each accumulator tile goes straight through AdamW against the p / m / v of the same elements.
+extern "C" int b200_wgrad_adamw(const void* dy, const void* x, int T, int M, int N, int ld_dy, int ld_x,
+                                const b200_wgrad_adamw_args* a, void* grad_out_f32, int pair, int force_bn, void* stream) {
+  using namespace b200;
+  using namespace b200::gemm;
+  B200_REQUIRE(a != nullptr && a->nseg >= 1 && a->nseg <= 3, "wgrad_adamw: 1..3 parameter segments");
+  B200_REQUIRE(a->hyper_dev && a->step_dev, "wgrad_adamw: hyper-parameters and step counter must be device pointers");
+  AdamwOperands o{};
+  int rows = 0;
+  for (int i = 0; i < a->nseg; ++i) {
+    B200_REQUIRE(a->p[i] && a->m[i] && a->v[i] && a->rows[i] > 0, "wgrad_adamw: segment %d incomplete", i);
+    B200_REQUIRE((reinterpret_cast<uintptr_t>(a->p[i]) | reinterpret_cast<uintptr_t>(a->m[i]) |
+                  reinterpret_cast<uintptr_t>(a->v[i])) % 16 == 0, "wgrad_adamw: p/m/v must be 16-byte aligned");
+    o.p[i] = a->p[i]; o.m[i] = a->m[i]; o.v[i] = a->v[i];
+    o.row0[i] = rows;
+    rows += a->rows[i];
+  }
+  for (int i = a->nseg; i < 4; ++i) o.row0[i] = rows;
+  B200_REQUIRE(rows == M, "wgrad_adamw: segments cover %d rows, the gradient has %d", rows, M);
+  B200_REQUIRE(!a->shadow_bf16 || reinterpret_cast<uintptr_t>(a->shadow_bf16) % 8 == 0, "wgrad_adamw: shadow alignment");
+  o.nseg = a->nseg; o.mode = a->mode;
+  o.shadow = reinterpret_cast<__nv_bfloat16*>(a->shadow_bf16);
+  o.hyper = a->hyper_dev; o.step = a->step_dev;
+  auto run = (pair && M >= 256) ? gemm2_run : gemm1_run;
+  return run(dy, x, grad_out_f32, nullptr, M, N, T, ld_dy, ld_x, N, 0, 1, 1, EPI_ADAMW, force_bn, 0, 0, 0, 0, &o, stream);
+}
+
+int b200::gemm::gemm2_run(const void* A, const void* B, void* C, const void* aux, int M, int N, int K, int lda, int ldb,
+                          int ldc, int ld_aux, int a_mn_major, int b_mn_major, int epilogue, int force_bn, int rope_S,
+                          int rope_dh, int rope_cols, int rope_ctx, const AdamwOperands* opt, void* stream) {
   using namespace b200;
   using namespace b200::gemm;
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm2: empty problem %dx%dx%d", M, N, K);
@@ -278,6 +319,9 @@ extern "C" int b200_gemm2_bf16_ex(const void* A, const void* B, void* C, const v
   p.C = C; p.aux = aux; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.ld_aux = ld_aux;
   p.num_m = ceil_div(M, BM); p.num_n = ceil_div(N, bn); p.num_k = ceil_div(K, BK);
   p.rope_S = rope_S; p.rope_dh = rope_dh; p.rope_cols = rope_cols; p.rope_ctx = rope_ctx;
+  p.opt = AdamwOperands{};
+  if (opt) p.opt = *opt;
+  B200_REQUIRE(epilogue != EPI_ADAMW || opt != nullptr, "gemm2: the AdamW epilogue needs its optimizer operands");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   switch (bn) {
     case 256: return dispatch_major2<256>(a_mn, b_mn, epilogue, tmA, tmB, p, s);

@@ -20,6 +20,24 @@ enum Epilogue : int {
   EPI_BF16_ROPE = 5,    // C bf16 = acc with RoPE applied to columns < rope_cols (fused QKV projection):
                         //   row r is token position r % rope_S, column c is element c % rope_dh of its head,
                         //   aux = fp32 cos/sin cache (2, rope_ctx, rope_dh/2)
+  EPI_ADAMW = 7,        // wgrad GEMM whose epilogue IS the optimizer: acc = dW tile; reads p, m, v of the same elements,
+                        //   applies AdamW and writes p, m, v and the bf16 GEMM shadow — the gradient never reaches HBM
+                        //   (C, when non-null, additionally receives it as fp32, for checks)
+};
+
+// Optimizer operands of EPI_ADAMW.  The GEMM's M rows are the rows of up to three parameters stacked in the order of
+// their fused forward GEMM (q|k|v, w1|w3): segment i covers rows [row0[i], row0[i+1]) and has its own p / m / v
+// (each a contiguous [rows_i, N] fp32 tensor); the bf16 shadow is the stacked [M, N] operand of the forward GEMM.
+struct AdamwOperands {
+  float* p[3];
+  float* m[3];
+  float* v[3];
+  int row0[4];
+  int nseg;
+  int mode;               // 0: course AdamW, 1: torch.optim.AdamW (same arithmetic as csrc/adamw.cu)
+  __nv_bfloat16* shadow;  // nullable
+  const float* hyper;     // device: lr, beta1, beta2, eps, weight_decay, grad_scale
+  const int* step;        // device: t of this update
 };
 
 struct Params {
@@ -29,7 +47,101 @@ struct Params {
   int ldc, ld_aux;
   int num_m, num_n, num_k;
   int rope_S, rope_dh, rope_cols, rope_ctx;
+  AdamwOperands opt;  // EPI_ADAMW only
 };
+
+// per-thread constants of the AdamW epilogue (computed once per kernel by each epilogue thread)
+struct AdamwConsts {
+  float lr, b1, b2, eps, wd, gscale, alpha_t, bc1, rsqrt_bc2;
+};
+__device__ __forceinline__ AdamwConsts adamw_consts(const AdamwOperands& o) {
+  AdamwConsts c;
+  c.lr = o.hyper[0]; c.b1 = o.hyper[1]; c.b2 = o.hyper[2]; c.eps = o.hyper[3]; c.wd = o.hyper[4]; c.gscale = o.hyper[5];
+  const float t = (float)(*o.step);
+  c.bc1 = 1.f - powf(c.b1, t);
+  const float bc2 = 1.f - powf(c.b2, t);
+  c.alpha_t = c.lr * sqrtf(bc2) / c.bc1;
+  c.rsqrt_bc2 = rsqrtf(bc2);
+  return c;
+}
+
+// AdamW on 32 consecutive elements of one parameter row (the thread's accumulator chunk = their gradient)
+__device__ __forceinline__ void adamw_chunk(const Params& p, const AdamwConsts& k, int row, int col0,
+                                            const uint32_t (&r)[32]) {
+  if (row >= p.M || col0 >= p.N) return;
+  const AdamwOperands& o = p.opt;
+  int s = 0;
+  if (o.nseg > 1 && row >= o.row0[1]) s = 1;
+  if (o.nseg > 2 && row >= o.row0[2]) s = 2;
+  // selects, not dynamic indexing: kernel parameters live in the constant bank and would be copied to local memory
+  const int r0 = s == 0 ? o.row0[0] : (s == 1 ? o.row0[1] : o.row0[2]);
+  const size_t off = (size_t)(row - r0) * p.N + col0;
+  float* pp = (s == 0 ? o.p[0] : (s == 1 ? o.p[1] : o.p[2])) + off;
+  float* mp = (s == 0 ? o.m[0] : (s == 1 ? o.m[1] : o.m[2])) + off;
+  float* vp = (s == 0 ? o.v[0] : (s == 1 ? o.v[1] : o.v[2])) + off;
+  __nv_bfloat16* sh = o.shadow ? o.shadow + (size_t)row * p.N + col0 : nullptr;
+  float* gout = p.C ? reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0 : nullptr;
+  const bool vec = (col0 + 32 <= p.N) && (p.N & 7) == 0;
+  if (vec) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {  // two halves of 16 elements: 12 vector loads in flight, then the math
+      f32x4 P[4], M[4], V[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        P[q] = *reinterpret_cast<const f32x4*>(pp + 16 * h + 4 * q);
+        M[q] = *reinterpret_cast<const f32x4*>(mp + 16 * h + 4 * q);
+        V[q] = *reinterpret_cast<const f32x4*>(vp + 16 * h + 4 * q);
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        float pv[4] = {P[q].x, P[q].y, P[q].z, P[q].w}, mv[4] = {M[q].x, M[q].y, M[q].z, M[q].w};
+        float vv[4] = {V[q].x, V[q].y, V[q].z, V[q].w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float gk = __uint_as_float(r[16 * h + 4 * q + e]) * k.gscale;
+          const float mk = k.b1 * mv[e] + (1.f - k.b1) * gk;
+          const float vk = k.b2 * vv[e] + (1.f - k.b2) * gk * gk;
+          float pk = pv[e];
+          if (o.mode == 0) {
+            pk -= k.alpha_t * mk / (sqrtf(vk) + k.eps);
+            pk -= k.lr * k.wd * pk;
+          } else {
+            pk *= (1.f - k.lr * k.wd);
+            pk -= (k.lr / k.bc1) * mk / (sqrtf(vk) * k.rsqrt_bc2 + k.eps);
+          }
+          mv[e] = mk; vv[e] = vk; pv[e] = pk;
+        }
+        *reinterpret_cast<f32x4*>(pp + 16 * h + 4 * q) = f32x4{pv[0], pv[1], pv[2], pv[3]};
+        *reinterpret_cast<f32x4*>(mp + 16 * h + 4 * q) = f32x4{mv[0], mv[1], mv[2], mv[3]};
+        *reinterpret_cast<f32x4*>(vp + 16 * h + 4 * q) = f32x4{vv[0], vv[1], vv[2], vv[3]};
+        if (sh) *reinterpret_cast<uint2*>(sh + 16 * h + 4 * q) = uint2{pack_bf16x2(pv[0], pv[1]), pack_bf16x2(pv[2], pv[3])};
+        if (gout)
+          *reinterpret_cast<f32x4*>(gout + 16 * h + 4 * q) =
+              f32x4{__uint_as_float(r[16 * h + 4 * q]), __uint_as_float(r[16 * h + 4 * q + 1]),
+                    __uint_as_float(r[16 * h + 4 * q + 2]), __uint_as_float(r[16 * h + 4 * q + 3])};
+      }
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {  // fully unrolled: r[] must stay in registers
+      if (col0 + j >= p.N) continue;
+      const float gk = __uint_as_float(r[j]) * k.gscale;
+      const float mk = k.b1 * mp[j] + (1.f - k.b1) * gk;
+      const float vk = k.b2 * vp[j] + (1.f - k.b2) * gk * gk;
+      float pk = pp[j];
+      if (o.mode == 0) {
+        pk -= k.alpha_t * mk / (sqrtf(vk) + k.eps);
+        pk -= k.lr * k.wd * pk;
+      } else {
+        pk *= (1.f - k.lr * k.wd);
+        pk -= (k.lr / k.bc1) * mk / (sqrtf(vk) * k.rsqrt_bc2 + k.eps);
+      }
+      mp[j] = mk; vp[j] = vk; pp[j] = pk;
+      if (sh) sh[j] = __float2bfloat16(pk);
+      if (gout) gout[j] = __uint_as_float(r[j]);
+    }
+  }
+}
 
 template <int EPI>
 __device__ __forceinline__ void store_chunk(const Params& p, int row, int col0, const uint32_t (&r)[32]) {
@@ -174,6 +286,14 @@ __device__ __forceinline__ void store_chunk(const Params& p, int row, int col0, 
   }
 }
 
+// host entry points of the two kernel families (gemm_sm100.cu: one CTA per tile; gemm2_sm100.cu: CTA pairs), shared by
+// the C ABI wrappers; `opt` is only read for EPI_ADAMW
+int gemm1_run(const void* A, const void* B, void* C, const void* aux, int M, int N, int K, int lda, int ldb, int ldc,
+              int ld_aux, int a_mn_major, int b_mn_major, int epilogue, int force_bn, int rope_S, int rope_dh,
+              int rope_cols, int rope_ctx, const AdamwOperands* opt, void* stream);
+int gemm2_run(const void* A, const void* B, void* C, const void* aux, int M, int N, int K, int lda, int ldb, int ldc,
+              int ld_aux, int a_mn_major, int b_mn_major, int epilogue, int force_bn, int rope_S, int rope_dh,
+              int rope_cols, int rope_ctx, const AdamwOperands* opt, void* stream);
 
 }  // namespace gemm
 }  // namespace b200

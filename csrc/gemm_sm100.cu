@@ -152,6 +152,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int ew = warp - 4;  // == warp % 4: TMEM lane quadrant this warp may access
     int acc = 0;
     uint32_t acc_phase = 0;
+    AdamwConsts ak;
+    if constexpr (EPI == EPI_ADAMW) ak = adamw_consts(p.opt);
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       const int m0 = (t % p.num_m) * BM;
       const int n0 = (t / p.num_m) * BN;
@@ -165,7 +167,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint32_t r[32];
         ptx::tmem_ld_32x32b_x32(t_row + c * 32, r);
         ptx::tmem_ld_wait();
-        store_chunk<EPI>(p, row, n0 + c * 32, r);
+        if constexpr (EPI == EPI_ADAMW) adamw_chunk(p, ak, row, n0 + c * 32, r);
+        else store_chunk<EPI>(p, row, n0 + c * 32, r);
       }
       ptx::tc_fence_before();
       __syncwarp();
@@ -232,6 +235,9 @@ static int dispatch_epi(int epi, const CUtensorMap& a, const CUtensorMap& b, con
     case EPI_BF16_ROPE:
       if constexpr (!A_MN && !B_MN) return launch<BN, A_MN, B_MN, EPI_BF16_ROPE>(a, b, p, s);
       break;
+    case EPI_ADAMW:
+      if constexpr (A_MN && B_MN) return launch<BN, A_MN, B_MN, EPI_ADAMW>(a, b, p, s);
+      break;
   }
   set_error("gemm: unsupported epilogue %d for this operand layout", epi);
   return B200_ERR_ARG;
@@ -263,6 +269,13 @@ extern "C" int b200_gemm_bf16(const void* A, const void* B, void* C, const void*
 extern "C" int b200_gemm_bf16_ex(const void* A, const void* B, void* C, const void* aux, int M, int N, int K, int lda,
                                  int ldb, int ldc, int ld_aux, int a_mn_major, int b_mn_major, int epilogue,
                                  int force_bn, int rope_S, int rope_dh, int rope_cols, int rope_ctx, void* stream) {
+  return b200::gemm::gemm1_run(A, B, C, aux, M, N, K, lda, ldb, ldc, ld_aux, a_mn_major, b_mn_major, epilogue, force_bn,
+                               rope_S, rope_dh, rope_cols, rope_ctx, nullptr, stream);
+}
+
+int b200::gemm::gemm1_run(const void* A, const void* B, void* C, const void* aux, int M, int N, int K, int lda, int ldb,
+                          int ldc, int ld_aux, int a_mn_major, int b_mn_major, int epilogue, int force_bn, int rope_S,
+                          int rope_dh, int rope_cols, int rope_ctx, const AdamwOperands* opt, void* stream) {
   using namespace b200;
   using namespace b200::gemm;
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
@@ -290,6 +303,9 @@ extern "C" int b200_gemm_bf16_ex(const void* A, const void* B, void* C, const vo
   p.C = C; p.aux = aux; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.ld_aux = ld_aux;
   p.num_m = ceil_div(M, BM); p.num_n = ceil_div(N, bn); p.num_k = ceil_div(K, BK);
   p.rope_S = rope_S; p.rope_dh = rope_dh; p.rope_cols = rope_cols; p.rope_ctx = rope_ctx;
+  p.opt = AdamwOperands{};
+  if (opt) p.opt = *opt;
+  B200_REQUIRE(epilogue != EPI_ADAMW || opt != nullptr, "gemm: the AdamW epilogue needs its optimizer operands");
   if (epilogue == EPI_BF16_ROPE)
     B200_REQUIRE(aux && rope_S > 0 && rope_dh > 0 && (rope_dh % 2) == 0 && rope_S <= rope_ctx && (rope_cols % 2) == 0,
                  "gemm: RoPE epilogue needs the cos/sin cache, S <= ctx and an even head dim");

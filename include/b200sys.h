@@ -42,6 +42,28 @@ int b200_gemm_bf16_ex(const void* A, const void* B, void* C, const void* aux, in
                       int ldc, int ld_aux, int a_mn_major, int b_mn_major, int epilogue, int force_bn, int rope_S,
                       int rope_dh, int rope_cols, int rope_ctx, void* stream);
 
+/* Weight-gradient GEMM whose epilogue is the optimizer.  dW[M, N] = dy^T x with dy: [T, M], x: [T, N] (bf16, row
+ * strides ld_dy / ld_x); the accumulator tile never becomes a gradient tensor: the epilogue reads p, m, v of the same
+ * elements, applies AdamW (mode 0: course arithmetic, 1: torch.optim.AdamW) and writes p, m, v and the bf16 GEMM
+ * shadow.  The M rows are the rows of 1..3 parameters stacked in the order of their fused forward GEMM (q|k|v, w1|w3);
+ * each segment has its own contiguous [rows_i, N] fp32 p / m / v, the shadow is the stacked [M, N] bf16 operand.
+ * hyper_dev: device floats lr, beta1, beta2, eps, weight_decay, grad_scale; step_dev: device int t of this update
+ * (advance it once per optimisation step with b200_incr_step).  grad_out_f32 (nullable, [M, N]) also receives dW.
+ * ref: the wgrad cuBLAS GEMM of Linear.backward (model.py:41) + the per-parameter AdamW (optimizer.py:50-86). */
+typedef struct {
+  float* p[3];
+  float* m[3];
+  float* v[3];
+  int rows[3];
+  int nseg;
+  int mode;
+  void* shadow_bf16;
+  const float* hyper_dev;
+  const int* step_dev;
+} b200_wgrad_adamw_args;
+int b200_wgrad_adamw(const void* dy, const void* x, int T, int M, int N, int ld_dy, int ld_x,
+                     const b200_wgrad_adamw_args* args, void* grad_out_f32, int pair, int force_bn, void* stream);
+
 /* ---- row softmax -------------------------------------------------------------------------------
  * out[r, :] = softmax(scale * in[r, :]) for `rows` rows of `cols` columns (row strides ld_in / ld_out in elements;
  * fp32 or bf16 in and out).  causal_period > 0: row r is query position r % causal_period and only sees columns

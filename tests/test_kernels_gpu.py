@@ -312,3 +312,48 @@ def test_materialized_attention_matches_oracle(N, D, causal, dtype):
     assert _rel_err(o, o_ref) < 1.5e-2
     for a, b in ((q, q2), (kk, k2), (v, v2)):
         assert _rel_err(a.grad, b.grad) < 3e-2
+
+
+# ------------------------------------------------------------------------------------------------ wgrad + AdamW epilogue
+@pytest.mark.parametrize("T,rows,N", [(512, (256,), 128), (2048, (1600, 1600, 1600), 1600), (1024, (640, 640), 320),
+                                      (300, (200,), 136), (2048, (1600,), 6400)])
+@pytest.mark.parametrize("pair", [False, True])
+def test_wgrad_adamw_epilogue(T, rows, N, pair):
+    """dW = dy^T x consumed by AdamW inside the GEMM epilogue == wgrad GEMM into a gradient tensor + the multi-tensor
+    AdamW kernel (same course arithmetic, optimizer.py:50-86): p, m, v to fp32 rounding, identical bf16 shadow."""
+    k = _k()
+    torch.manual_seed(0)
+    M = sum(rows)
+    if pair and M < 256:
+        pytest.skip("CTA pairs need at least one 256-row tile")
+    dy = _bf(torch.randn(T, M, device="cuda") * 0.1)
+    x = _bf(torch.randn(T, N, device="cuda"))
+    ps = [torch.randn(r, N, device="cuda") * 0.05 for r in rows]
+    ms = [torch.randn(r, N, device="cuda") * 0.01 for r in rows]
+    vs = [torch.rand(r, N, device="cuda") * 1e-3 for r in rows]
+    # reference: gradient tensor, then the multi-tensor kernel
+    g = k.wgrad(dy, x)
+    p_ref, m_ref, v_ref = [t.clone() for t in ps], [t.clone() for t in ms], [t.clone() for t in vs]
+    sh_ref = [torch.empty_like(t, dtype=torch.bfloat16) for t in ps]
+    gs, r0 = [], 0
+    for r in rows:
+        gs.append(g[r0:r0 + r].contiguous())
+        r0 += r
+    launch = k.AdamWLaunch(p_ref, gs, m_ref, v_ref, sh_ref, step0=3, mode=0)
+    launch.set_hyper(3e-3, 0.9, 0.95, 1e-8, 0.1)
+    launch.launch()
+    # fused
+    dh = k.DeviceHyper("cuda", step0=3)
+    dh.set(3e-3, 0.9, 0.95, 1e-8, 0.1)
+    shadow = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    gout = torch.empty(M, N, device="cuda")
+    k.wgrad_adamw(dy, x, ps, ms, vs, shadow, dh, mode=0, grad_out=gout, pair=pair)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(gout, g, rtol=1e-5, atol=1e-5)
+    r0 = 0
+    for i, r in enumerate(rows):
+        torch.testing.assert_close(ms[i], m_ref[i], rtol=1e-5, atol=1e-7)
+        torch.testing.assert_close(vs[i], v_ref[i], rtol=1e-5, atol=1e-9)
+        torch.testing.assert_close(ps[i], p_ref[i], rtol=1e-5, atol=1e-6)
+        assert _rel_err(shadow[r0:r0 + r], sh_ref[i]) < 1e-3
+        r0 += r

@@ -22,7 +22,8 @@ nvidia-smi topo -m > gpurun_out/mg_topo.log 2>&1
 run pytest_mg 900 B200SYS_X=1 -- python -m pytest tests/test_multigpu.py -x -q -p no:cacheprovider
 run zero_kernel 300 B200SYS_X=1 -- $(trun) -m cs336_a2_systems_b200.bench.zero --sizes-mb 100 1000 --json gpurun_out/zero_kernel_n$N.json
 run allreduce 300 B200SYS_X=1 -- $(trun) -m cs336_a2_systems_b200.bench.allreduce --sizes-mb 0.064 1 10 100 1000 --json gpurun_out/allreduce_n$N.json
-for cfg in "auto auto" "0 0" "0 1" "3 0" "3 1" "1 0"; do
+IFS=';' read -ra CFGS <<< "${MG_CFGS:-auto auto;0 0;0 1;3 0;3 1;1 0}"   # "<zero variant> <defer>" pairs
+for cfg in "${CFGS[@]}"; do
   set -- $cfg
   v=$1; d=$2
   vflag=""; [ "$v" != "auto" ] && vflag="--zero-variant $v"
