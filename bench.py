@@ -40,6 +40,9 @@ def parse_args():
     ap.add_argument("--ctx", type=int, default=512)
     ap.add_argument("--vocab", type=int, default=10000)
     ap.add_argument("--bucket-mb", type=float, default=100.0)
+    ap.add_argument("--ddp", choices=["bucketed", "individual"], default="bucketed",
+                    help="N>1: bucketed overlapped DDP (the headline) or one overlapped all-reduce per parameter "
+                         "(reference DDP class, ddp_bucketed_overlapped_sharded.py:217-248)")
     ap.add_argument("--no-graph", action="store_true", help="ours: do not capture the step in a CUDA graph")
     ap.add_argument("--comm", default=None, help="ours: gradient backend override (symm | c10d)")
     ap.add_argument("--sharded", action="store_true",
@@ -59,8 +62,9 @@ def parse_args():
     ap.add_argument("--watchdog-s", type=float, default=420.0,
                     help="abort the whole process (exit code 3, one JSON error line) if the run has not finished "
                          "after this many seconds, instead of sitting in a collective until its 10-minute timeout")
-    ap.add_argument("--no-opt-in-bwd", action="store_true",
-                    help="ours, 1 GPU: keep AdamW a separate pass after backward instead of the wgrad GEMM epilogues")
+    ap.add_argument("--opt-in-bwd", action="store_true",
+                    help="ours, 1 GPU: apply AdamW inside the wgrad GEMM epilogues instead of a separate pass after "
+                         "backward (measured slower on B200, see DESIGN.md)")
     ap.add_argument("--no-overlap", action="store_true",
                     help="ours: run the optimizer after backward instead of overlapping it with backward")
     return ap.parse_args()
@@ -131,13 +135,16 @@ def build_ours(args, rank, ws, dev):
 
     torch.manual_seed(1234 + rank)  # DDP broadcasts rank 0's weights
     model = build_lm(args.model, vocab_size=args.vocab, context_length=args.ctx, device=dev)
-    if ws > 1:
+    if ws > 1 and args.ddp == "individual":
+        from cs336_a2_systems_b200.parallel import DDPIndividualParameters
+        model = DDPIndividualParameters(model, backend=args.comm)
+    elif ws > 1:
         model = DDPBucketed(model, bucket_size_mb=args.bucket_mb, backend=args.comm)
     kw = dict(lr=1e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
     fused_sharded = False
     symm_backend = getattr(getattr(model, "_reducer", None), "kind", "") == "symm"
     explicit = args.sharded or args.optimizer == "sharded"
-    shard = ws > 1 and (explicit or (args.optimizer == "auto" and symm_backend))
+    shard = ws > 1 and (explicit or (args.optimizer == "auto" and symm_backend and args.ddp == "bucketed"))
     # measured at 2 and 8 GPUs (profiles/r2): deferring costs more than it hides, so 'auto' keeps it off
     defer = args.defer_gather == "1"
     opt = None
@@ -169,7 +176,7 @@ def build_ours(args, rank, ws, dev):
     trainer = Trainer(model, opt, autocast=True,
                       cuda_graph=not args.no_graph and (bucket_fused or not args.shard_effective),
                       overlap_optimizer=not args.no_overlap and not args.shard_effective,
-                      graph_warmup_steps=2, optimizer_in_backward=False if args.no_opt_in_bwd else None)
+                      graph_warmup_steps=2, optimizer_in_backward=True if args.opt_in_bwd else None)
     state = {"launches_per_step": 0, "trainer": trainer, "optimizer": opt}
 
     def step_device(x, y):
@@ -210,7 +217,9 @@ def build_reference(args, rank, ws, dev):
                                         num_layers=cfg["num_layers"], num_heads=cfg["num_heads"], d_ff=cfg["d_ff"],
                                         rope_theta=10000.0)
     model = model.to(dev)
-    ddp = ref.DDP_Bucketed(model, bucket_size_mb=args.bucket_mb) if ws > 1 else None
+    ddp = None
+    if ws > 1:
+        ddp = ref.DDP(model) if args.ddp == "individual" else ref.DDP_Bucketed(model, bucket_size_mb=args.bucket_mb)
     kw = dict(lr=1e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
     if args.sharded and ws > 1:
         opt = ref.ShardedStateOptimizer(model.parameters(), ref.AdamW, **kw)
@@ -351,14 +360,14 @@ def _main(args):
         else:
             placement = "AdamW replicated"
         out = {
-            "metric": f"{args.model.upper()} LM train tokens/s (bucketed DDP, bf16 autocast, {placement})",
+            "metric": f"{args.model.upper()} LM train tokens/s ({'per-parameter' if args.ddp == 'individual' else 'bucketed'} DDP, bf16 autocast, {placement})",
             "value": round(value, 1), "unit": "tokens/s", "n_gpus": ws, "steps": args.steps, "warmup": n_warm,
             "ms_per_step": round(ms_per_step, 3), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic tokens, random-init weights",
             "impl": args.impl,
             "config": {"model": args.model, **cfg, "vocab": args.vocab, "seq_len": args.ctx,
                        "global_batch": ws * args.batch, "per_gpu_batch": args.batch,
-                       "parallelism": f"dp{ws}", "bucket_size_mb": args.bucket_mb,
+                       "parallelism": f"dp{ws}", "ddp": args.ddp, "bucket_size_mb": args.bucket_mb,
                        "optimizer": placement,
                        "l2": "no flush: ~30 GB working set per step >> 126 MB L2", **extra},
             "e2e": {"value": round(e2e_value, 1), "unit": "tokens/s", "ms_per_step": round(ms_e2e / args.steps, 3),

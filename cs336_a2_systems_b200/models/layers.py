@@ -16,6 +16,8 @@ Parameter names, shapes, init and ``parameters()`` order are unchanged, so check
 
 from __future__ import annotations
 
+import os
+
 import math
 
 import torch
@@ -131,6 +133,10 @@ class SwiGLU(nn.Module):
             if not torch.is_grad_enabled():  # serving / eval: the gate runs in the GEMM epilogue
                 h = native.swiglu_linear_nograd(x, self.w1.weight, self.w3.weight)
                 return native.linear(h, (self.w2.weight,))
+            if os.environ.get("B200SYS_FUSE_SWIGLU", "1") == "1":
+                y = native.swiglu_ffn(x, self.w1.weight, self.w3.weight, self.w2.weight)  # gate in the GEMM epilogues
+                if y is not None:
+                    return y
             ab = native.linear(x, (self.w1.weight, self.w3.weight))  # one GEMM → [.., 2*d_ff]
             return native.linear(native.swiglu(ab), (self.w2.weight,))
         return self.w2(F_ref.silu(self.w1(x)) * self.w3(x))

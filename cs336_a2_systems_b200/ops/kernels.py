@@ -21,6 +21,7 @@ BF16, F32 = 0, 1
 _DT = {torch.bfloat16: BF16, torch.float32: F32}
 
 EPI_BF16, EPI_F32, EPI_F32_ACC, EPI_BF16_SWIGLU, EPI_F32_RESID, EPI_BF16_ROPE, EPI_F32_T, EPI_ADAMW = 0, 1, 2, 3, 4, 5, 6, 7
+EPI_SWIGLU_FWD, EPI_SWIGLU_BWD = 8, 9
 
 #: route eligible GEMMs through the CTA-pair (cta_group::2) kernel
 GEMM_PAIR = _environ.get("B200SYS_GEMM_PAIR", "auto")  # "auto": per-shape choice, "1": always when legal, "0": never
@@ -94,15 +95,21 @@ def gemm_supported(a: Tensor, b: Tensor) -> bool:
 
 
 def wgrad(dy: Tensor, x: Tensor, out: Tensor | None = None) -> Tensor:
-    """``dW[N_out, K_in] = dyᵀ · x`` (fp32).  A tall result (N_out > K_in) is computed as its wide transpose
-    ``xᵀ · dy`` with the transposed-store epilogue: the tile-width dimension gets the long side (256-wide
-    tiles run ~1.4x faster than 128-wide ones) and the stores are fully coalesced."""
+    """``dW[N_out, K_in] = dyᵀ · x`` (fp32).  Always computed as the transpose ``xᵀ · dy`` with the transposed-store
+    epilogue (``EPI_F32_T``): a thread owns one row of dWᵀ, so for every accumulator register the 32 lanes of a warp
+    write 32 consecutive floats of one dW row — one coalesced 128-byte store, where the row-per-thread fp32 epilogue
+    scatters each 16-byte vector store over 32 cache lines (measured 0.72-0.80x of cuBLAS on the square / wide
+    wgrads, `profiles/r2/gemm_vs_cublas_xl.json`)."""
     n_out, k_in = dy.shape[1], x.shape[1]
-    if n_out > k_in:
-        if out is None:
-            out = torch.empty(n_out, k_in, dtype=torch.float32, device=dy.device)
-        return gemm(x, dy, a_mn=True, b_mn=True, epilogue=EPI_F32_T, out=out)
-    return gemm(dy, x, a_mn=True, b_mn=True, epilogue=EPI_F32, out=out)
+    if out is None:
+        out = torch.empty(n_out, k_in, dtype=torch.float32, device=dy.device)
+    if os_environ_flag("B200SYS_WGRAD_PLAIN"):
+        return gemm(dy, x, a_mn=True, b_mn=True, epilogue=EPI_F32, out=out)
+    return gemm(x, dy, a_mn=True, b_mn=True, epilogue=EPI_F32_T, out=out)
+
+
+def os_environ_flag(name: str) -> bool:
+    return _environ.get(name, "0") == "1"
 
 
 def gemm(a: Tensor, b: Tensor, *, a_mn: bool = False, b_mn: bool = False, epilogue: int = EPI_BF16,
@@ -145,6 +152,48 @@ def gemm(a: Tensor, b: Tensor, *, a_mn: bool = False, b_mn: bool = False, epilog
                                    c_int(rope_cols), c_int(rope_ctx), stream_ptr()), "gemm")
     _count()
     return out
+
+
+def swiglu_up_supported(x2: Tensor, w13: Tensor) -> bool:
+    """The fused up-projection needs CTA pairs (>= 256 rows) and d_ff a multiple of 128."""
+    F2 = w13.shape[0]
+    return x2.shape[0] >= 256 and F2 % 256 == 0 and gemm_supported(x2, w13)
+
+
+def gemm_swiglu_fwd(x2: Tensor, w13: Tensor):
+    """``x2``: bf16 [T, K]; ``w13``: bf16 [2F, K] = w1 stacked on w3.  ONE GEMM whose epilogue applies the gate:
+    returns ``(g, ab)`` with ``g = silu(x w1ᵀ) * (x w3ᵀ)`` (bf16 [T, F]) and the pre-activations ``ab`` (bf16 [T, 2F],
+    ``a | b``) the backward needs (``EPI_SWIGLU_FWD``: each 256-column tile is 128 rows of w1 next to the same 128
+    rows of w3, so no interleaved weight copy is needed)."""
+    T, K = x2.shape
+    F2 = w13.shape[0]
+    F = F2 // 2
+    g = torch.empty(T, F, dtype=torch.bfloat16, device=x2.device)
+    ab = torch.empty(T, F2, dtype=torch.bfloat16, device=x2.device)
+    check(_lib().b200_gemm2_bf16_ex(p(x2), p(w13), p(g), p(ab), c_int(T), c_int(F2), c_int(K), c_int(x2.stride(0)),
+                                    c_int(w13.stride(0)), c_int(F), c_int(F2), c_int(0), c_int(0),
+                                    c_int(EPI_SWIGLU_FWD), c_int(256), c_int(0), c_int(0), c_int(0), c_int(0),
+                                    stream_ptr()), "gemm_swiglu_fwd")
+    _count()
+    return g, ab
+
+
+def gemm_swiglu_bwd(dy2: Tensor, w2: Tensor, ab: Tensor) -> Tensor:
+    """``dy2``: bf16 [T, d]; ``w2``: bf16 [d, F] (the down-projection, read as an MN-major B operand); ``ab``: the saved
+    pre-activations.  The dgrad GEMM ``dg = dy · w2`` with the gate's backward in its epilogue (``EPI_SWIGLU_BWD``):
+    returns ``dab = (da | db)`` bf16 [T, 2F]; ``dg`` never reaches memory."""
+    T, d = dy2.shape
+    F = w2.shape[1]
+    assert w2.shape[0] == d and ab.shape == (T, 2 * F) and ab.is_contiguous()
+    dab = torch.empty(T, 2 * F, dtype=torch.bfloat16, device=dy2.device)
+    pair_ok = T >= 256
+    use_pair, bn = _plan_gemm(T, F, True, pair_ok) if GEMM_PAIR == "auto" else (pair_ok and GEMM_PAIR == "1", 0)
+    fn = _lib().b200_gemm2_bf16_ex if use_pair else _lib().b200_gemm_bf16_ex
+    check(fn(p(dy2), p(w2), p(dab), p(ab), c_int(T), c_int(F), c_int(d), c_int(dy2.stride(0)), c_int(w2.stride(0)),
+             c_int(2 * F), c_int(2 * F), c_int(0), c_int(1), c_int(EPI_SWIGLU_BWD), c_int(bn), c_int(0), c_int(0),
+             c_int(0), c_int(0), stream_ptr()), "gemm_swiglu_bwd")
+    _count()
+    return dab
 
 
 # ------------------------------------------------------------------------------------------------
@@ -451,10 +500,11 @@ def wgrad_adamw(dy: Tensor, x: Tensor, params, ms, vs, shadow: Tensor | None, dh
     a.hyper, a.step = dh.hyper.data_ptr(), dh.step.data_ptr()
     if grad_out is not None:
         assert grad_out.dtype == torch.float32 and grad_out.is_contiguous() and tuple(grad_out.shape) == (M, N)
+    # the kernel computes the transpose (rows = N input features, columns = the M stacked parameter rows)
     if pair is None:
-        use_pair, bn = _plan_gemm(M, N, True, M >= 256) if GEMM_PAIR == "auto" else (GEMM_PAIR == "1" and M >= 256, 0)
+        use_pair, bn = _plan_gemm(N, M, True, N >= 256) if GEMM_PAIR == "auto" else (GEMM_PAIR == "1" and N >= 256, 0)
     else:
-        use_pair, bn = pair, 0
+        use_pair, bn = pair and N >= 256, 0
     check(_lib().b200_wgrad_adamw(p(dy), p(x), c_int(T), c_int(M), c_int(N), c_int(dy.stride(0)), c_int(x.stride(0)),
                                   ctypes.byref(a), p(grad_out), c_int(int(use_pair)), c_int(bn), stream_ptr()),
           "wgrad_adamw")

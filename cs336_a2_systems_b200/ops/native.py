@@ -152,39 +152,44 @@ class LinearFn(torch.autograd.Function):
             dx = dx.view(ctx.x_shape)
             if ctx.x_dtype != BF16:
                 dx = dx.to(ctx.x_dtype)
-        ws = ctx.weights
-        need = ctx.needs_input_grad[3:]
-        # optimizer in the wgrad epilogue (AdamW.fuse_into_backward): the whole group must belong to one fused group,
-        # each weight mirrored by exactly this shadow, nothing accumulated into .grad yet
-        grp = getattr(ws[0], "_b200_bwd_opt", None)
-        if grp is not None and all(need) and all(getattr(w, "_b200_bwd_opt", None) is grp and w.grad is None and
-                                                 len(getattr(w, "_b200_shadow_slices", ())) == 1 for w in ws) and \
-                wb.is_contiguous() and torch.is_grad_enabled() is False:
-            grp.wgrad(dy2, x2, ws, wb)
-            return (dx, None, None, *([None] * len(ws)))
-        if len(ws) > 1 and all(need):
-            joint = grad_slots.claim_group(ws)
-            if joint is not None:
-                kernels.wgrad(dy2, x2, out=joint)
-                dws, r0 = [], 0
-                for w in ws:
-                    dws.append(joint[r0:r0 + w.shape[0]])
-                    r0 += w.shape[0]
-                return (dx, None, None, *dws)
-        dws = []
-        r0 = 0
-        for i, w in enumerate(ws):
-            n_i = w.shape[0]
-            if need[i]:
-                dst = grad_slots.claim(w)
-                dyi = dy2[:, r0:r0 + n_i]  # column slice: MN-major A operand with lda = N
-                if dyi.data_ptr() % 16 != 0:
-                    dyi = dyi.contiguous()
-                dws.append(kernels.wgrad(dyi, x2, out=dst))
-            else:
-                dws.append(None)
-            r0 += n_i
-        return (dx, None, None, *dws)
+        return (dx, None, None, *_weight_grads(ctx.weights, ctx.needs_input_grad[3:], dy2, x2, wb))
+
+
+def _weight_grads(ws, need, dy2: Tensor, x2: Tensor, wb: Tensor) -> list:
+    """Weight gradients of a (fused group of) linear map(s) ``y = x2 · wbᵀ`` for ``dy2``: one entry per weight.
+    Either the optimizer runs inside the wgrad GEMM (all entries None), or the group's slots are adjacent (one GEMM),
+    or one wgrad GEMM per weight straight into its gradient slot."""
+    # optimizer in the wgrad epilogue (AdamW.fuse_into_backward): the whole group must belong to one fused group,
+    # each weight mirrored by exactly this shadow, nothing accumulated into .grad yet
+    grp = getattr(ws[0], "_b200_bwd_opt", None)
+    if grp is not None and all(need) and all(getattr(w, "_b200_bwd_opt", None) is grp and w.grad is None and
+                                             len(getattr(w, "_b200_shadow_slices", ())) == 1 for w in ws) and \
+            wb.is_contiguous() and not torch.is_grad_enabled():
+        grp.wgrad(dy2, x2, ws, wb)
+        return [None] * len(ws)
+    if len(ws) > 1 and all(need):
+        joint = grad_slots.claim_group(ws)
+        if joint is not None:
+            kernels.wgrad(dy2, x2, out=joint)
+            dws, r0 = [], 0
+            for w in ws:
+                dws.append(joint[r0:r0 + w.shape[0]])
+                r0 += w.shape[0]
+            return dws
+    dws = []
+    r0 = 0
+    for i, w in enumerate(ws):
+        n_i = w.shape[0]
+        if need[i]:
+            dst = grad_slots.claim(w)
+            dyi = dy2[:, r0:r0 + n_i]  # column slice: MN-major A operand with lda = N
+            if dyi.data_ptr() % 16 != 0:
+                dyi = dyi.contiguous()
+            dws.append(kernels.wgrad(dyi, x2, out=dst))
+        else:
+            dws.append(None)
+        r0 += n_i
+    return dws
 
 
 def linear(x: Tensor, weights: tuple[Tensor, ...], rope: tuple | None = None) -> Tensor:
@@ -319,6 +324,55 @@ class SwiGLUFn(torch.autograd.Function):
 
 def swiglu(ab: Tensor) -> Tensor:
     return SwiGLUFn.apply(ab)
+
+
+class SwiGLUFFNFn(torch.autograd.Function):
+    """The whole feed-forward block ``w2(silu(w1 x) * w3 x)`` with the gate inside the GEMM epilogues:
+
+    forward   ``g, ab = gemm_swiglu_fwd(x, [w1; w3])`` — ONE GEMM writes the gated product and the pre-activations;
+              ``y = g · w2ᵀ``
+    backward  ``dab = gemm_swiglu_bwd(dy, w2, ab)`` — the dgrad GEMM of w2 applies the gate's backward in its epilogue
+              (``dg`` never reaches memory); ``dx = dab · [w1; w3]``; wgrads of w2 (from ``g``) and w1‖w3 (from ``dab``)
+
+    Saved for backward: ``x``, ``ab``, ``g`` and the two weight shadows — what the unfused chain saves too."""
+
+    @staticmethod
+    def forward(ctx, x: Tensor, wb13: Tensor, wb2: Tensor, w1: Tensor, w3: Tensor, w2: Tensor):
+        K = wb13.shape[1]
+        x2 = _to_bf16_2d(x, K)
+        g, ab = kernels.gemm_swiglu_fwd(x2, wb13)
+        y = kernels.gemm(g, wb2)
+        ctx.save_for_backward(x2, ab, g, wb13, wb2)
+        ctx.weights = (w1, w3, w2)
+        ctx.x_shape, ctx.x_dtype = x.shape, x.dtype
+        return y.view(*x.shape[:-1], wb2.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy: Tensor):
+        x2, ab, g, wb13, wb2 = ctx.saved_tensors
+        w1, w3, w2 = ctx.weights
+        dy2 = _to_bf16_2d(dy, wb2.shape[0])
+        need = ctx.needs_input_grad
+        dab = kernels.gemm_swiglu_bwd(dy2, wb2, ab)
+        dx = None
+        if need[0]:
+            dx = kernels.gemm(dab, wb13, b_mn=True).view(ctx.x_shape)
+            if ctx.x_dtype != BF16:
+                dx = dx.to(ctx.x_dtype)
+        (dw2,) = _weight_grads((w2,), (need[5],), dy2, g, wb2)
+        dw1, dw3 = _weight_grads((w1, w3), (need[3], need[4]), dab, x2, wb13)
+        return dx, None, None, dw1, dw3, dw2
+
+
+def swiglu_ffn(x: Tensor, w1: Tensor, w3: Tensor, w2: Tensor) -> Tensor | None:
+    """Fused training path of the feed-forward block, or None when the shape cannot take it (fewer than 256 tokens,
+    d_ff not a multiple of 128) — the caller then runs the unfused chain."""
+    wb13 = weight_shadow((w1, w3))
+    K = w1.shape[1]
+    T = x.numel() // K
+    if T < 256 or (2 * w1.shape[0]) % 256 != 0 or w1.shape[0] != w3.shape[0]:
+        return None
+    return SwiGLUFFNFn.apply(x, wb13, weight_shadow((w2,)), w1, w3, w2)
 
 
 def gated_shadow(w1: Tensor, w3: Tensor) -> Tensor:

@@ -130,12 +130,15 @@ class Trainer:
         if max_grad_norm is not None and hasattr(getattr(optimizer, "_symm", None), "_reduce_bucket"):
             raise ValueError("the bucket-fused sharded AdamW applies the update as each bucket's gradients arrive; "
                              "it cannot be combined with global gradient-norm clipping")
-        # Single-process CUDA training with this package's AdamW and no clipping: run the optimizer of the Linear weights
-        # inside their wgrad GEMM epilogues (their gradients never reach HBM); everything else still goes through step()
+        # Optional (single-process CUDA training with this package's AdamW, no clipping): run the optimizer of the Linear
+        # weights inside their wgrad GEMM epilogues — their gradients never reach HBM; everything else still goes
+        # through step().  Off by default: on B200 the epilogue (26 B per accumulator element through 8 epilogue warps)
+        # sustains 2.4 TB/s, the separate multi-tensor kernel 6 TB/s, so the fused GEMM is slower than GEMM + AdamW
+        # (w1|w3 wgrad: 0.225 ms vs 0.160 ms, profiles/r2/gemm_vs_cublas_xl.json; XL step 48.7 vs 41.8 ms).
         self.optimizer_in_backward = False
         want = optimizer_in_backward
         if want is None:
-            want = os.environ.get("B200SYS_OPT_IN_BWD", "1") == "1"
+            want = os.environ.get("B200SYS_OPT_IN_BWD", "0") == "1"
         if want and self.device.type == "cuda" and not self._is_ddp and max_grad_norm is None and \
                 hasattr(optimizer, "fuse_into_backward") and autocast:
             self.optimizer_in_backward = optimizer.fuse_into_backward(model) > 0

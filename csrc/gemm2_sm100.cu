@@ -36,7 +36,7 @@ struct Cfg2 {
 };
 
 template <int BN, bool A_MN, bool B_MN, int EPI>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128 + 32 * EpiWarps<EPI>::N, 1)
 gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params p) {
   using C = Cfg2<BN>;
   constexpr int STAGES = C::STAGES;
@@ -64,7 +64,7 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
     for (int a = 0; a < 2; ++a) {
       ptx::mbar_init(&tfull_bar[a], 1);   // multicast tcgen05.commit
-      ptx::mbar_init(&tempty_bar[a], 8);  // 4 epilogue warps of each CTA
+      ptx::mbar_init(&tempty_bar[a], 2 * EpiWarps<EPI>::N);  // the epilogue warps of both CTAs
     }
     ptx::fence_mbar_init();
   }
@@ -92,7 +92,10 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       uint32_t phase = 0;
       for (int t = cluster_id; t < total_tiles; t += num_clusters) {
         const int m0 = ((t % num_m2) * 2 + (int)cta_rank) * BM;
-        const int n0 = (t / num_m2) * BN + (int)cta_rank * (BN / 2);
+        // this CTA's half of the B tile; EPI_SWIGLU_FWD: rank 0 takes 128 rows of w1, rank 1 the same rows of w3
+        // (row F + ... of the stacked weight), so a tile's accumulator is [a of 128 hidden units | their b]
+        const int n0 = EPI == EPI_SWIGLU_FWD ? (t / num_m2) * (BN / 2) + (int)cta_rank * (p.N >> 1)
+                                             : (t / num_m2) * BN + (int)cta_rank * (BN / 2);
         for (int kb = 0; kb < p.num_k; ++kb) {
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
           const uint32_t lead_full = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
@@ -151,7 +154,9 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
   } else if (warp >= 4) {
     // ================================ epilogue (both CTAs) ================================
-    const int ew = warp - 4;
+    const int ew = (warp - 4) & 3;
+    constexpr int NGRP = EpiWarps<EPI>::N / 4;  // column groups: group g takes the 32-column chunks c = g, g + NGRP, …
+    const int grp = (warp - 4) >> 2;
     int acc = 0;
     uint32_t acc_phase = 0;
     AdamwConsts ak;
@@ -163,14 +168,28 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       ptx::tc_fence_after();
       const int row = m0 + ew * 32 + lane;
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BN;
+      if constexpr (EPI == EPI_SWIGLU_FWD) {
+        const int hid0 = (t / num_m2) * (BN / 2);  // first hidden unit of this tile
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        if (n0 + c * 32 >= p.N) break;
-        uint32_t r[32];
-        ptx::tmem_ld_32x32b_x32(t_row + c * 32, r);
-        ptx::tmem_ld_wait();
-        if constexpr (EPI == EPI_ADAMW) adamw_chunk(p, ak, row, n0 + c * 32, r);
-        else store_chunk<EPI>(p, row, n0 + c * 32, r);
+        for (int c = 0; c < BN / 64; ++c) {
+          if (hid0 + c * 32 >= (p.N >> 1)) break;
+          uint32_t ra[32], rb[32];
+          ptx::tmem_ld_32x32b_x32(t_row + c * 32, ra);
+          ptx::tmem_ld_32x32b_x32(t_row + BN / 2 + c * 32, rb);
+          ptx::tmem_ld_wait();
+          swiglu_fwd_chunk(p, row, hid0 + c * 32, ra, rb);
+        }
+      } else {
+#pragma unroll 1
+        for (int c = grp; c < BN / 32; c += NGRP) {
+          if (n0 + c * 32 >= p.N) break;
+          uint32_t r[32];
+          ptx::tmem_ld_32x32b_x32(t_row + c * 32, r);
+          ptx::tmem_ld_wait();
+          if constexpr (EPI == EPI_ADAMW) adamw_chunk_t(p, ak, row, n0 + c * 32, r);
+          else if constexpr (EPI == EPI_SWIGLU_BWD) swiglu_bwd_chunk(p, row, n0 + c * 32, r);
+          else store_chunk<EPI>(p, row, n0 + c * 32, r);
+        }
       }
       ptx::tc_fence_before();
       __syncwarp();
@@ -217,7 +236,7 @@ static int launch2(const CUtensorMap& tmA, const CUtensorMap& tmB, const Params&
   const int tiles = ceil_div(p.num_m, 2) * p.num_n;
   const int clusters = num_sms() / 2;
   const int grid = 2 * (tiles < clusters ? tiles : clusters);
-  B200_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kThreads2), C::SMEM_BYTES, stream, tmA, tmB, p));
+  B200_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(128 + 32 * EpiWarps<EPI>::N), C::SMEM_BYTES, stream, tmA, tmB, p));
   return 0;
 }
 
@@ -234,6 +253,12 @@ static int dispatch_epi2(int epi, const CUtensorMap& a, const CUtensorMap& b, co
       break;
     case EPI_ADAMW:
       if constexpr (A_MN && B_MN) return launch2<BN, A_MN, B_MN, EPI_ADAMW>(a, b, p, s);
+      break;
+    case EPI_SWIGLU_FWD:
+      if constexpr (!A_MN && !B_MN && BN == 256) return launch2<BN, A_MN, B_MN, EPI_SWIGLU_FWD>(a, b, p, s);
+      break;
+    case EPI_SWIGLU_BWD:
+      if constexpr (!A_MN && B_MN) return launch2<BN, A_MN, B_MN, EPI_SWIGLU_BWD>(a, b, p, s);
       break;
   }
   set_error("gemm2: epilogue %d not available in the CTA-pair kernel for this layout", epi);
@@ -286,8 +311,10 @@ extern "C" int b200_wgrad_adamw(const void* dy, const void* x, int T, int M, int
   o.nseg = a->nseg; o.mode = a->mode;
   o.shadow = reinterpret_cast<__nv_bfloat16*>(a->shadow_bf16);
   o.hyper = a->hyper_dev; o.step = a->step_dev;
-  auto run = (pair && M >= 256) ? gemm2_run : gemm1_run;
-  return run(dy, x, grad_out_f32, nullptr, M, N, T, ld_dy, ld_x, N, 0, 1, 1, EPI_ADAMW, force_bn, 0, 0, 0, 0, &o, stream);
+  // the GEMM runs on the transpose (dWᵀ = xᵀ·dy: rows = input features, columns = stacked parameter rows) so that the
+  // epilogue's accesses to p / m / v are coalesced — see adamw_chunk_t
+  auto run = (pair && N >= 256) ? gemm2_run : gemm1_run;
+  return run(x, dy, grad_out_f32, nullptr, N, M, T, ld_x, ld_dy, N, 0, 1, 1, EPI_ADAMW, force_bn, 0, 0, 0, 0, &o, stream);
 }
 
 int b200::gemm::gemm2_run(const void* A, const void* B, void* C, const void* aux, int M, int N, int K, int lda, int ldb,
@@ -318,6 +345,11 @@ int b200::gemm::gemm2_run(const void* A, const void* B, void* C, const void* aux
   Params p;
   p.C = C; p.aux = aux; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.ld_aux = ld_aux;
   p.num_m = ceil_div(M, BM); p.num_n = ceil_div(N, bn); p.num_k = ceil_div(K, BK);
+  if (epilogue == EPI_SWIGLU_FWD) {
+    B200_REQUIRE(bn == 256 && (N % 256) == 0 && !a_mn && !b_mn && aux != nullptr,
+                 "gemm2: the SwiGLU forward epilogue needs 256-wide tiles, N = 2F with F a multiple of 128, K-major operands");
+    p.num_n = (N / 2) / 128;  // one tile = 128 hidden units = 128 rows of w1 + the same 128 rows of w3
+  }
   p.rope_S = rope_S; p.rope_dh = rope_dh; p.rope_cols = rope_cols; p.rope_ctx = rope_ctx;
   p.opt = AdamwOperands{};
   if (opt) p.opt = *opt;

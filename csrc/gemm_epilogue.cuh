@@ -20,6 +20,13 @@ enum Epilogue : int {
   EPI_BF16_ROPE = 5,    // C bf16 = acc with RoPE applied to columns < rope_cols (fused QKV projection):
                         //   row r is token position r % rope_S, column c is element c % rope_dh of its head,
                         //   aux = fp32 cos/sin cache (2, rope_ctx, rope_dh/2)
+  EPI_SWIGLU_FWD = 8,   // training forward of the SwiGLU up-projection (CTA-pair kernel, BN = 256): a tile holds the gate
+                        //   pre-activations a of 128 hidden units in accumulator columns 0..127 and their up-projections b
+                        //   in columns 128..255 (the B tile is fetched from w1 rows and w3 rows of the stacked weight);
+                        //   C bf16 [M, F] = silu(a)*b, aux (written!) bf16 [M, 2F] = a | b kept for the backward.  N = 2F.
+  EPI_SWIGLU_BWD = 9,   // dgrad GEMM of the down-projection with the gate's backward in its epilogue: acc = dg tile,
+                        //   aux bf16 [M, 2F] = a | b, C bf16 [M, 2F] = da | db with da = dg*b*(s + a*s*(1-s)), db = dg*a*s,
+                        //   s = sigmoid(a).  N = F (dg never reaches HBM).
   EPI_ADAMW = 7,        // wgrad GEMM whose epilogue IS the optimizer: acc = dW tile; reads p, m, v of the same elements,
                         //   applies AdamW and writes p, m, v and the bf16 GEMM shadow — the gradient never reaches HBM
                         //   (C, when non-null, additionally receives it as fp32, for checks)
@@ -65,70 +72,53 @@ __device__ __forceinline__ AdamwConsts adamw_consts(const AdamwOperands& o) {
   return c;
 }
 
-// AdamW on 32 consecutive elements of one parameter row (the thread's accumulator chunk = their gradient)
-__device__ __forceinline__ void adamw_chunk(const Params& p, const AdamwConsts& k, int row, int col0,
-                                            const uint32_t (&r)[32]) {
+// AdamW epilogue, transposed orientation.  The GEMM computes dWᵀ (rows = input features, columns = the stacked
+// parameter rows), so a thread (= one TMEM lane = one dWᵀ row) holds 32 consecutive dW ROWS of one dW column: for a
+// fixed register the 32 lanes of the warp touch 32 consecutive floats of p / m / v — every load and store is one
+// fully coalesced 128-byte request.  (The row-per-thread orientation costs 32 L1 wavefronts per 16-byte vector
+// instruction: measured 2x slower than running the optimizer as a separate kernel.)
+//   p.M = input features (columns of dW), p.N = stacked parameter rows, parameters are contiguous [rows_i, p.M].
+__device__ __forceinline__ void adamw_chunk_t(const Params& p, const AdamwConsts& k, int row, int col0,
+                                              const uint32_t (&r)[32]) {
   if (row >= p.M || col0 >= p.N) return;
   const AdamwOperands& o = p.opt;
-  int s = 0;
-  if (o.nseg > 1 && row >= o.row0[1]) s = 1;
-  if (o.nseg > 2 && row >= o.row0[2]) s = 2;
-  // selects, not dynamic indexing: kernel parameters live in the constant bank and would be copied to local memory
-  const int r0 = s == 0 ? o.row0[0] : (s == 1 ? o.row0[1] : o.row0[2]);
-  const size_t off = (size_t)(row - r0) * p.N + col0;
-  float* pp = (s == 0 ? o.p[0] : (s == 1 ? o.p[1] : o.p[2])) + off;
-  float* mp = (s == 0 ? o.m[0] : (s == 1 ? o.m[1] : o.m[2])) + off;
-  float* vp = (s == 0 ? o.v[0] : (s == 1 ? o.v[1] : o.v[2])) + off;
-  __nv_bfloat16* sh = o.shadow ? o.shadow + (size_t)row * p.N + col0 : nullptr;
-  float* gout = p.C ? reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0 : nullptr;
-  const bool vec = (col0 + 32 <= p.N) && (p.N & 7) == 0;
-  if (vec) {
+  const size_t ld = (size_t)p.M;
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {  // two halves of 16 elements: 12 vector loads in flight, then the math
-      f32x4 P[4], M[4], V[4];
+  for (int h = 0; h < 2; ++h) {  // halves of 16 registers: 48 independent loads in flight, then the math
+    float P[16], M[16], V[16];
+    uint32_t off[16];  // element offset inside one parameter (< 2^32)
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        P[q] = *reinterpret_cast<const f32x4*>(pp + 16 * h + 4 * q);
-        M[q] = *reinterpret_cast<const f32x4*>(mp + 16 * h + 4 * q);
-        V[q] = *reinterpret_cast<const f32x4*>(vp + 16 * h + 4 * q);
-      }
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        float pv[4] = {P[q].x, P[q].y, P[q].z, P[q].w}, mv[4] = {M[q].x, M[q].y, M[q].z, M[q].w};
-        float vv[4] = {V[q].x, V[q].y, V[q].z, V[q].w};
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float gk = __uint_as_float(r[16 * h + 4 * q + e]) * k.gscale;
-          const float mk = k.b1 * mv[e] + (1.f - k.b1) * gk;
-          const float vk = k.b2 * vv[e] + (1.f - k.b2) * gk * gk;
-          float pk = pv[e];
-          if (o.mode == 0) {
-            pk -= k.alpha_t * mk / (sqrtf(vk) + k.eps);
-            pk -= k.lr * k.wd * pk;
-          } else {
-            pk *= (1.f - k.lr * k.wd);
-            pk -= (k.lr / k.bc1) * mk / (sqrtf(vk) * k.rsqrt_bc2 + k.eps);
-          }
-          mv[e] = mk; vv[e] = vk; pv[e] = pk;
-        }
-        *reinterpret_cast<f32x4*>(pp + 16 * h + 4 * q) = f32x4{pv[0], pv[1], pv[2], pv[3]};
-        *reinterpret_cast<f32x4*>(mp + 16 * h + 4 * q) = f32x4{mv[0], mv[1], mv[2], mv[3]};
-        *reinterpret_cast<f32x4*>(vp + 16 * h + 4 * q) = f32x4{vv[0], vv[1], vv[2], vv[3]};
-        if (sh) *reinterpret_cast<uint2*>(sh + 16 * h + 4 * q) = uint2{pack_bf16x2(pv[0], pv[1]), pack_bf16x2(pv[2], pv[3])};
-        if (gout)
-          *reinterpret_cast<f32x4*>(gout + 16 * h + 4 * q) =
-              f32x4{__uint_as_float(r[16 * h + 4 * q]), __uint_as_float(r[16 * h + 4 * q + 1]),
-                    __uint_as_float(r[16 * h + 4 * q + 2]), __uint_as_float(r[16 * h + 4 * q + 3])};
-      }
+    for (int j = 0; j < 16; ++j) {
+      const int dwrow = col0 + 16 * h + j;
+      int s = 0;
+      if (o.nseg > 1 && dwrow >= o.row0[1]) s = 1;
+      if (o.nseg > 2 && dwrow >= o.row0[2]) s = 2;
+      // selects, not dynamic indexing: kernel parameters live in the constant bank
+      const int r0 = s == 0 ? o.row0[0] : (s == 1 ? o.row0[1] : o.row0[2]);
+      const float* pb = s == 0 ? o.p[0] : (s == 1 ? o.p[1] : o.p[2]);
+      const float* mb = s == 0 ? o.m[0] : (s == 1 ? o.m[1] : o.m[2]);
+      const float* vb = s == 0 ? o.v[0] : (s == 1 ? o.v[1] : o.v[2]);
+      off[j] = (uint32_t)((size_t)(dwrow - r0) * ld + row);
+      const bool ok = dwrow < p.N;
+      P[j] = ok ? pb[off[j]] : 0.f;
+      M[j] = ok ? mb[off[j]] : 0.f;
+      V[j] = ok ? vb[off[j]] : 0.f;
     }
-  } else {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {  // fully unrolled: r[] must stay in registers
-      if (col0 + j >= p.N) continue;
-      const float gk = __uint_as_float(r[j]) * k.gscale;
-      const float mk = k.b1 * mp[j] + (1.f - k.b1) * gk;
-      const float vk = k.b2 * vp[j] + (1.f - k.b2) * gk * gk;
-      float pk = pp[j];
+    for (int j = 0; j < 16; ++j) {
+      const int dwrow = col0 + 16 * h + j;
+      if (dwrow >= p.N) continue;
+      int s = 0;
+      if (o.nseg > 1 && dwrow >= o.row0[1]) s = 1;
+      if (o.nseg > 2 && dwrow >= o.row0[2]) s = 2;
+      float* pb = s == 0 ? o.p[0] : (s == 1 ? o.p[1] : o.p[2]);
+      float* mb = s == 0 ? o.m[0] : (s == 1 ? o.m[1] : o.m[2]);
+      float* vb = s == 0 ? o.v[0] : (s == 1 ? o.v[1] : o.v[2]);
+      const float g = __uint_as_float(r[16 * h + j]);
+      const float gk = g * k.gscale;
+      const float mk = k.b1 * M[j] + (1.f - k.b1) * gk;
+      const float vk = k.b2 * V[j] + (1.f - k.b2) * gk * gk;
+      float pk = P[j];
       if (o.mode == 0) {
         pk -= k.alpha_t * mk / (sqrtf(vk) + k.eps);
         pk -= k.lr * k.wd * pk;
@@ -136,12 +126,101 @@ __device__ __forceinline__ void adamw_chunk(const Params& p, const AdamwConsts& 
         pk *= (1.f - k.lr * k.wd);
         pk -= (k.lr / k.bc1) * mk / (sqrtf(vk) * k.rsqrt_bc2 + k.eps);
       }
-      mp[j] = mk; vp[j] = vk; pp[j] = pk;
-      if (sh) sh[j] = __float2bfloat16(pk);
-      if (gout) gout[j] = __uint_as_float(r[j]);
+      pb[off[j]] = pk;
+      mb[off[j]] = mk;
+      vb[off[j]] = vk;
+      if (o.shadow) o.shadow[(size_t)dwrow * ld + row] = __float2bfloat16(pk);
+      if (p.C) reinterpret_cast<float*>(p.C)[(size_t)dwrow * p.ldc + row] = g;
     }
   }
 }
+
+// ---- SwiGLU gate in the GEMM epilogues (training) ------------------------------------------------------------
+__device__ __forceinline__ void st_bf16x32(__nv_bfloat16* dst, const float (&v)[32], bool vec, int valid) {
+  if (vec) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      u32x4 o;
+      o.x = pack_bf16x2(v[8 * q + 0], v[8 * q + 1]);
+      o.y = pack_bf16x2(v[8 * q + 2], v[8 * q + 3]);
+      o.z = pack_bf16x2(v[8 * q + 4], v[8 * q + 5]);
+      o.w = pack_bf16x2(v[8 * q + 6], v[8 * q + 7]);
+      *reinterpret_cast<u32x4*>(dst + 8 * q) = o;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (j < valid) dst[j] = __float2bfloat16(v[j]);
+  }
+}
+// ra / rb: 32 gate / up pre-activations of hidden units hid0..hid0+31 of one row
+__device__ __forceinline__ void swiglu_fwd_chunk(const Params& p, int row, int hid0, const uint32_t (&ra)[32],
+                                                 const uint32_t (&rb)[32]) {
+  const int F = p.N >> 1;
+  if (row >= p.M || hid0 >= F) return;
+  const int valid = F - hid0 < 32 ? F - hid0 : 32;
+  float a[32], b[32], g[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    a[j] = __uint_as_float(ra[j]);
+    b[j] = __uint_as_float(rb[j]);
+    g[j] = a[j] / (1.f + __expf(-a[j])) * b[j];
+  }
+  __nv_bfloat16* gp = reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + hid0;
+  __nv_bfloat16* abp = reinterpret_cast<__nv_bfloat16*>(const_cast<void*>(p.aux)) + (size_t)row * p.ld_aux + hid0;
+  const bool vec = valid == 32 && (p.ldc & 7) == 0 && (p.ld_aux & 7) == 0 && (F & 7) == 0;
+  st_bf16x32(gp, g, vec, valid);
+  st_bf16x32(abp, a, vec, valid);
+  st_bf16x32(abp + F, b, vec, valid);
+}
+// r: 32 columns col0..col0+31 of the dg tile of one row
+__device__ __forceinline__ void swiglu_bwd_chunk(const Params& p, int row, int col0, const uint32_t (&r)[32]) {
+  const int F = p.N;
+  if (row >= p.M || col0 >= F) return;
+  const int valid = F - col0 < 32 ? F - col0 : 32;
+  const __nv_bfloat16* abp = reinterpret_cast<const __nv_bfloat16*>(p.aux) + (size_t)row * p.ld_aux + col0;
+  __nv_bfloat16* dp = reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + col0;
+  const bool vec = valid == 32 && (p.ldc & 7) == 0 && (p.ld_aux & 7) == 0 && (F & 7) == 0;
+  float a[32], b[32];
+  if (vec) {
+    u32x4 av[4], bv[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {  // eight 16-byte loads issued up front
+      av[q] = *reinterpret_cast<const u32x4*>(abp + 8 * q);
+      bv[q] = *reinterpret_cast<const u32x4*>(abp + F + 8 * q);
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t aw[4] = {av[q].x, av[q].y, av[q].z, av[q].w}, bw[4] = {bv[q].x, bv[q].y, bv[q].z, bv[q].w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 fa = unpack_bf16x2(aw[e]), fb = unpack_bf16x2(bw[e]);
+        a[8 * q + 2 * e] = fa.x; a[8 * q + 2 * e + 1] = fa.y;
+        b[8 * q + 2 * e] = fb.x; b[8 * q + 2 * e + 1] = fb.y;
+      }
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      a[j] = j < valid ? __bfloat162float(abp[j]) : 0.f;
+      b[j] = j < valid ? __bfloat162float(abp[F + j]) : 0.f;
+    }
+  }
+  float da[32], db[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    const float dg = __uint_as_float(r[j]);
+    const float sg = 1.f / (1.f + __expf(-a[j]));
+    da[j] = dg * b[j] * (sg + a[j] * sg * (1.f - sg));
+    db[j] = dg * a[j] * sg;
+  }
+  st_bf16x32(dp, da, vec, valid);
+  st_bf16x32(dp + F, db, vec, valid);
+}
+
+// epilogue warps per CTA: the optimizer epilogue streams 26 bytes per accumulator element and needs twice the loads
+// in flight of a plain store epilogue
+template <int EPI> struct EpiWarps { static constexpr int N = EPI == EPI_ADAMW ? 8 : 4; };
 
 template <int EPI>
 __device__ __forceinline__ void store_chunk(const Params& p, int row, int col0, const uint32_t (&r)[32]) {

@@ -40,7 +40,7 @@ struct Cfg {
 };
 
 template <int BN, bool A_MN, bool B_MN, int EPI>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(128 + 32 * EpiWarps<EPI>::N, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params p) {
   using C = Cfg<BN>;
   constexpr int STAGES = C::STAGES;
@@ -66,7 +66,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int a = 0; a < 2; ++a) {
       ptx::mbar_init(&tfull_bar[a], 1);
-      ptx::mbar_init(&tempty_bar[a], 4);  // one arrive per epilogue warp
+      ptx::mbar_init(&tempty_bar[a], EpiWarps<EPI>::N);  // one arrive per epilogue warp
     }
     ptx::fence_mbar_init();
   }
@@ -149,7 +149,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else if (warp >= 4) {
     // ================================ epilogue ================================
-    const int ew = warp - 4;  // == warp % 4: TMEM lane quadrant this warp may access
+    const int ew = (warp - 4) & 3;  // == warp % 4: TMEM lane quadrant this warp may access
+    constexpr int NGRP = EpiWarps<EPI>::N / 4;  // column groups: group g takes the 32-column chunks c = g, g + NGRP, …
+    const int grp = (warp - 4) >> 2;
     int acc = 0;
     uint32_t acc_phase = 0;
     AdamwConsts ak;
@@ -162,12 +164,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int row = m0 + ew * 32 + lane;
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BN;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
+      for (int c = grp; c < BN / 32; c += NGRP) {
         if (n0 + c * 32 >= p.N) break;  // warp-uniform
         uint32_t r[32];
         ptx::tmem_ld_32x32b_x32(t_row + c * 32, r);
         ptx::tmem_ld_wait();
-        if constexpr (EPI == EPI_ADAMW) adamw_chunk(p, ak, row, n0 + c * 32, r);
+        if constexpr (EPI == EPI_ADAMW) adamw_chunk_t(p, ak, row, n0 + c * 32, r);
+        else if constexpr (EPI == EPI_SWIGLU_BWD) swiglu_bwd_chunk(p, row, n0 + c * 32, r);
         else store_chunk<EPI>(p, row, n0 + c * 32, r);
       }
       ptx::tc_fence_before();
@@ -213,7 +216,7 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Params& 
   B200_ENSURE_DYN_SMEM(kern, C::SMEM_BYTES);
   const int tiles = p.num_m * p.num_n;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  B200_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kThreads), C::SMEM_BYTES, stream, tmA, tmB, p));
+  B200_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(128 + 32 * EpiWarps<EPI>::N), C::SMEM_BYTES, stream, tmA, tmB, p));
   return 0;
 }
 
@@ -237,6 +240,9 @@ static int dispatch_epi(int epi, const CUtensorMap& a, const CUtensorMap& b, con
       break;
     case EPI_ADAMW:
       if constexpr (A_MN && B_MN) return launch<BN, A_MN, B_MN, EPI_ADAMW>(a, b, p, s);
+      break;
+    case EPI_SWIGLU_BWD:
+      if constexpr (!A_MN && B_MN) return launch<BN, A_MN, B_MN, EPI_SWIGLU_BWD>(a, b, p, s);
       break;
   }
   set_error("gemm: unsupported epilogue %d for this operand layout", epi);

@@ -8,6 +8,7 @@
 #include "ptx.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 #include <mutex>
 
 namespace b200 {
@@ -192,6 +193,98 @@ __global__ void __launch_bounds__(128) rmsnorm_bwd_dx_kernel(const TDY* __restri
   }
 }
 
+// dx AND the dw partial sums in one pass (the split above re-reads dy and x for dw: +20 MB and one more launch per
+// norm).  Persistent: gridDim.x CTAs of 128 threads walk the rows with stride gridDim.x; the NEXT row's dy, x and
+// incoming residual gradient are already in flight (second register set) while the current row is reduced and
+// written, and the gain vector w stays in registers for the whole kernel.  Each thread owns VPT float4 columns and
+// accumulates dw for them over its rows; partial[blockIdx.x][:] is reduced by colsum4_kernel afterwards.
+template <typename TDY, int VPT>
+struct RowRegs {
+  f32x4 g[VPT], xv[VPT], dr[VPT];
+};
+template <typename TDY, int VPT>
+__device__ __forceinline__ void rms_load_row(RowRegs<TDY, VPT>& R, const TDY* __restrict__ dy, const float* __restrict__ x,
+                                             const float* __restrict__ dres_in, int r, int d, int nvec) {
+  const size_t base = (size_t)r * d;
+#pragma unroll
+  for (int v = 0; v < VPT; ++v) {
+    const int c = threadIdx.x + 128 * v;
+    if (c < nvec) {
+      R.g[v] = ld_dy4<TDY>(dy, base + 4 * c);
+      R.xv[v] = *reinterpret_cast<const f32x4*>(x + base + 4 * c);
+      if (dres_in) R.dr[v] = *reinterpret_cast<const f32x4*>(dres_in + base + 4 * c);
+    }
+  }
+}
+template <typename TDY, int VPT>
+__device__ __forceinline__ void rms_process_row(RowRegs<TDY, VPT>& R, const f32x4 (&wv)[VPT], f32x4 (&acc)[VPT], float rs,
+                                                const float* __restrict__ dres_in, float* __restrict__ dx,
+                                                __nv_bfloat16* __restrict__ dx_bf16, int r, int d, int nvec, float* red) {
+  const size_t base = (size_t)r * d;
+  float dot = 0.f;
+#pragma unroll
+  for (int v = 0; v < VPT; ++v) {
+    const int c = threadIdx.x + 128 * v;
+    if (c < nvec) {
+      f32x4& g = R.g[v];
+      const f32x4& xv = R.xv[v];
+      acc[v].x += g.x * xv.x * rs; acc[v].y += g.y * xv.y * rs; acc[v].z += g.z * xv.z * rs; acc[v].w += g.w * xv.w * rs;
+      g.x *= wv[v].x; g.y *= wv[v].y; g.z *= wv[v].z; g.w *= wv[v].w;
+      dot += g.x * xv.x + g.y * xv.y + g.z * xv.z + g.w * xv.w;
+    }
+  }
+  dot = block_sum(dot, red) * rs / (float)d;  // mean(g * xhat)
+  const float k2 = rs * rs * dot;
+#pragma unroll
+  for (int v = 0; v < VPT; ++v) {
+    const int c = threadIdx.x + 128 * v;
+    if (c < nvec) {
+      const f32x4& g = R.g[v];
+      const f32x4& xv = R.xv[v];
+      f32x4 o{rs * g.x - k2 * xv.x, rs * g.y - k2 * xv.y, rs * g.z - k2 * xv.z, rs * g.w - k2 * xv.w};
+      if (dres_in) { o.x += R.dr[v].x; o.y += R.dr[v].y; o.z += R.dr[v].z; o.w += R.dr[v].w; }
+      if (dx) *reinterpret_cast<f32x4*>(dx + base + 4 * c) = o;
+      if (dx_bf16) *reinterpret_cast<uint2*>(dx_bf16 + base + 4 * c) = uint2{pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w)};
+    }
+  }
+}
+template <typename TDY, int VPT>
+__global__ void __launch_bounds__(128) rmsnorm_bwd_fused_kernel(const TDY* __restrict__ dy, const float* __restrict__ x,
+                                                                const float* __restrict__ w, const float* __restrict__ rstd,
+                                                                const float* __restrict__ dres_in, float* __restrict__ dx,
+                                                                __nv_bfloat16* __restrict__ dx_bf16,
+                                                                float* __restrict__ partial, int T, int d) {
+  __shared__ float red[32];
+  ptx::griddep_launch();
+  const int nvec = d >> 2;
+  const int G = gridDim.x;
+  f32x4 wv[VPT], acc[VPT];
+#pragma unroll
+  for (int v = 0; v < VPT; ++v) {
+    const int c = threadIdx.x + 128 * v;
+    acc[v] = f32x4{0.f, 0.f, 0.f, 0.f};
+    wv[v] = c < nvec ? *reinterpret_cast<const f32x4*>(w + 4 * c) : f32x4{0.f, 0.f, 0.f, 0.f};  // parameters: not produced by the previous kernel
+  }
+  ptx::griddep_wait();
+  RowRegs<TDY, VPT> A, B;
+  int r = blockIdx.x;
+  if (r < T) rms_load_row<TDY, VPT>(A, dy, x, dres_in, r, d, nvec);
+  while (r < T) {
+    if (r + G < T) rms_load_row<TDY, VPT>(B, dy, x, dres_in, r + G, d, nvec);
+    rms_process_row<TDY, VPT>(A, wv, acc, rstd[r], dres_in, dx, dx_bf16, r, d, nvec, red);
+    r += G;
+    if (r >= T) break;
+    if (r + G < T) rms_load_row<TDY, VPT>(A, dy, x, dres_in, r + G, d, nvec);
+    rms_process_row<TDY, VPT>(B, wv, acc, rstd[r], dres_in, dx, dx_bf16, r, d, nvec, red);
+    r += G;
+  }
+#pragma unroll
+  for (int v = 0; v < VPT; ++v) {
+    const int c = threadIdx.x + 128 * v;
+    if (c < nvec) *reinterpret_cast<f32x4*>(partial + (size_t)blockIdx.x * d + 4 * c) = acc[v];
+  }
+}
+
 // partial[chunk][j] = sum over the chunk's rows of dy[r,j] * x[r,j] * rstd[r]
 template <typename TDY>
 __global__ void __launch_bounds__(128) rmsnorm_bwd_dw_kernel(const TDY* __restrict__ dy, const float* __restrict__ x,
@@ -305,6 +398,30 @@ extern "C" int b200_rmsnorm_bwd(const void* dy, int dy_dtype, const float* x, co
                          reinterpret_cast<uintptr_t>(dres_in) | reinterpret_cast<uintptr_t>(dx) |
                          reinterpret_cast<uintptr_t>(dx_bf16)) & 15) == 0;
   if ((d % 8) == 0 && d <= 128 * 24 && aligned) {
+    static int fused_mode = -1;
+    if (fused_mode < 0) {
+      const char* e = getenv("B200SYS_RMSNORM_BWD");
+      fused_mode = (e && e[0] == 's') ? 0 : 1;  // "split": the two-kernel form (A/B measurements)
+    }
+    if (fused_mode && d <= 128 * 4 * 6) {
+      // one pass: dx + per-CTA dw partials (grid = workspace rows, so the scratch contract holds), then the column sum
+#define LAUNCH_F(TDY, VPL)                                                                                         \
+  B200_CHECK_CUDA(launch_pdl(rmsnorm_bwd_fused_kernel<TDY, VPL>, dim3(grid), dim3(128), 0, s,                       \
+                             reinterpret_cast<const TDY*>(dy), x, w, rstd, dres_in, dx, dxb, scratch, T, d))
+#define BY_DT_F(VPL)                                                   \
+  do {                                                                 \
+    if (dy_dtype == B200_BF16) LAUNCH_F(__nv_bfloat16, VPL);           \
+    else LAUNCH_F(float, VPL);                                         \
+  } while (0)
+      if (d <= 512 * 2) BY_DT_F(2);
+      else if (d <= 512 * 4) BY_DT_F(4);
+      else BY_DT_F(6);
+#undef BY_DT_F
+#undef LAUNCH_F
+      B200_CHECK_CUDA(launch_pdl(colsum4_kernel, dim3(ceil_div(d, 64)), dim3(256), 0, s, (const float*)scratch, dw, grid, d,
+                                 dw_accumulate));
+      return 0;
+    }
     // fast path; the dw partial matrix has `chunks` <= workspace rows, so the scratch contract holds
     const int rows_per_chunk = std::max(16, ceil_div(T, grid));
     const int chunks = ceil_div(T, rows_per_chunk);

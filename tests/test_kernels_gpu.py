@@ -324,7 +324,7 @@ def test_wgrad_adamw_epilogue(T, rows, N, pair):
     k = _k()
     torch.manual_seed(0)
     M = sum(rows)
-    if pair and M < 256:
+    if pair and N < 256:
         pytest.skip("CTA pairs need at least one 256-row tile")
     dy = _bf(torch.randn(T, M, device="cuda") * 0.1)
     x = _bf(torch.randn(T, N, device="cuda"))
@@ -357,3 +357,28 @@ def test_wgrad_adamw_epilogue(T, rows, N, pair):
         torch.testing.assert_close(ps[i], p_ref[i], rtol=1e-5, atol=1e-6)
         assert _rel_err(shadow[r0:r0 + r], sh_ref[i]) < 1e-3
         r0 += r
+
+
+# ------------------------------------------------------------------------------------------------ SwiGLU in the GEMM epilogues
+@pytest.mark.parametrize("T,K,F", [(256, 128, 128), (2048, 1600, 6400), (512, 320, 896), (300, 256, 384)])
+def test_gemm_swiglu_training_epilogues(T, K, F):
+    """Forward: ONE GEMM over [w1; w3] whose epilogue writes silu(a)*b and keeps a | b; backward: the dgrad GEMM of the
+    down-projection applies the gate's backward in its epilogue.  Against fp32 PyTorch."""
+    k = _k()
+    torch.manual_seed(0)
+    x = _bf(torch.randn(T, K, device="cuda"))
+    w13 = _bf(torch.randn(2 * F, K, device="cuda") / math.sqrt(K))
+    assert k.swiglu_up_supported(x, w13)
+    g, ab = k.gemm_swiglu_fwd(x, w13)
+    ref_ab = x.float() @ w13.float().t()
+    a, b = ref_ab[:, :F], ref_ab[:, F:]
+    assert _rel_err(ab, ref_ab) < 6e-3
+    assert _rel_err(g, torch.nn.functional.silu(a) * b) < 8e-3
+    # backward epilogue, against autograd through the bf16-rounded pre-activations the kernel reads
+    d = 192
+    dy = _bf(torch.randn(T, d, device="cuda"))
+    w2 = _bf(torch.randn(d, F, device="cuda") / math.sqrt(d))
+    dab = k.gemm_swiglu_bwd(dy, w2, ab)
+    abf = ab.float().requires_grad_(True)
+    (torch.nn.functional.silu(abf[:, :F]) * abf[:, F:]).backward(dy.float() @ w2.float())
+    assert _rel_err(dab, abf.grad) < 8e-3

@@ -17,4 +17,4 @@ run fa_check 200 python tools/fa_check.py --json gpurun_out/fa_check.json
 run bench 200 python bench.py --steps 10 --warmup 3
 run smoke 200 python __graft_entry__.py smoke
 run gemm 400 python -m cs336_a2_systems_b200.bench.gemm --model xl --json gpurun_out/gemm_vs_cublas_xl.json
-run bench_noopt 200 python bench.py --steps 10 --warmup 3 --no-opt-in-bwd
+run bench_optbwd 200 python bench.py --steps 10 --warmup 3 --opt-in-bwd
