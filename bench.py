@@ -53,7 +53,7 @@ def parse_args():
                          "per-bucket NVLink reduce kernel (every rank still ends the step with all updated fp32 "
                          "parameters); 'replicated' = all-reduce then full AdamW on every rank; 'auto' = sharded "
                          "whenever the NVLink backend is available (all ranks agree on the outcome)")
-    ap.add_argument("--defer-gather", choices=["auto", "0", "1"], default="auto",
+    ap.add_argument("--defer-gather", choices=["auto", "0", "1", "lazy"], default="auto",
                     help="ours, sharded: refresh the fp32 replicas of Linear weights under the NEXT forward instead "
                          "of inside the backward-overlapped bucket kernels (bf16 GEMM shadows and fp32-read "
                          "parameters are always distributed at once); 'auto' = off (measured slower at 2 and 8 GPUs)")
@@ -146,7 +146,7 @@ def build_ours(args, rank, ws, dev):
     explicit = args.sharded or args.optimizer == "sharded"
     shard = ws > 1 and (explicit or (args.optimizer == "auto" and symm_backend and args.ddp == "bucketed"))
     # measured at 2 and 8 GPUs (profiles/r2): deferring costs more than it hides, so 'auto' keeps it off
-    defer = args.defer_gather == "1"
+    defer = "lazy" if args.defer_gather == "lazy" else args.defer_gather == "1"
     opt = None
     if shard:
         from cs336_a2_systems_b200.parallel import ShardedOptimizer
@@ -196,7 +196,8 @@ def build_ours(args, rank, ws, dev):
              "bucket_fused_reduce_scatter_adamw_allgather": bucket_fused,
              "optimizer_in_wgrad_epilogue": trainer.optimizer_in_backward,
              "zero_kernel_variant": getattr(sym, "variant", None) if bucket_fused else None,
-             "deferred_fp32_param_gather": bool(getattr(sym, "defer", False)) if bucket_fused else None,
+             "deferred_fp32_param_gather": (("lazy (only on sync_params/state_dict)" if getattr(sym, "lazy", False)
+                                             else bool(getattr(sym, "defer", False))) if bucket_fused else None),
              "comm": getattr(getattr(model, "_reducer", None), "kind", "none")}
     return step_device, step_e2e, launches_now, state, extra
 

@@ -26,6 +26,7 @@ import argparse
 import json
 import os
 import sys
+import time
 
 import torch
 
@@ -99,9 +100,21 @@ def run(shapes, dtypes, impls, iters, warmup, ref=None):
                 torch.cuda.reset_peak_memory_stats()
                 with ClockSampler(0, period_ms=50) as clk:
                     r = _bench_impl(fn, q, k, v, n_it, warmup)
+                peak_mib = round(torch.cuda.max_memory_allocated() / 2 ** 20, 1)
+                clocks = clk.summary()
+                if not clocks.get("samples") and r.get("fwd_ms"):
+                    # the timed region was shorter than one sampling period: record the clocks of the same kernel run
+                    # back to back for 0.3 s (a number without a clock record counts as unmeasured)
+                    with ClockSampler(0, period_ms=50) as clk2, torch.no_grad():
+                        t_end = time.perf_counter() + 0.3
+                        while time.perf_counter() < t_end:
+                            for _ in range(20):
+                                fn(q, k, v)
+                            torch.cuda.synchronize()
+                    clocks = dict(clk2.summary(), note="sampled over a 0.3 s back-to-back re-run of the forward")
                 ff, fb = _flops(1, BH, N, D, True)
                 row = dict(impl=impl, heads=BH, seq=N, d=D, dtype=str(dt).split(".")[-1], **r,
-                           peak_mem_mib=round(torch.cuda.max_memory_allocated() / 2 ** 20, 1), clocks=clk.summary())
+                           peak_mem_mib=peak_mib, clocks=clocks)
                 if r.get("fwd_ms"):
                     row["fwd_tflops"] = ff / r["fwd_ms"] / 1e9
                 if r.get("bwd_ms"):

@@ -52,14 +52,22 @@ def _graph_time(fns, iters: int) -> float:
                 f()
         g.replay()
         s.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(s)
-        for _ in range(iters):
-            g.replay()
-        e1.record(s)
-        s.synchronize()
+
+        def timed(n):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(s)
+            for _ in range(n):
+                g.replay()
+            e1.record(s)
+            s.synchronize()
+            return e0.elapsed_time(e1)
+
+        ms = timed(iters)
+        # long enough (>= 0.25 s) for the clock sampler to see the region it vouches for
+        n = max(iters, int(250.0 / max(ms / iters, 1e-3)))
+        ms, iters = timed(n), n
     torch.cuda.current_stream().wait_stream(s)
-    return e0.elapsed_time(e1) / (iters * len(fns))
+    return ms / (iters * len(fns))
 
 
 def bench_one(kind: str, M: int, N: int, K: int, iters: int = 20, force_bn: int = 0, pair: bool | None = None):

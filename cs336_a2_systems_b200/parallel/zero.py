@@ -130,8 +130,14 @@ class BucketFusedAdamW:
             self.variant = 3 if (have_mc and self.ws > 2) else 0
         else:
             self.variant = int(v) if have_mc else 0
+        #: CTAs per bucket kernel (0 = one per SM): fewer CTAs leave more of each SM's issue slots and memory queues to
+        #: the backward GEMMs the kernel overlaps with
+        self.blocks = int(os.environ.get("B200SYS_ZERO_BLOCKS", "0"))
         if defer_fp32_gather is None:
             defer_fp32_gather = os.environ.get("B200SYS_ZERO_DEFER", "0") == "1"
+        #: "lazy": the fp32 replicas of Linear weights a rank does not own are refreshed only by sync_params() /
+        #: state_dict() (fp32 master weights live sharded with the optimizer state, as in ZeRO with bf16 parameters)
+        self.lazy = defer_fp32_gather == "lazy"
         self.defer = bool(defer_fp32_gather)
         sh = os.environ.get("B200SYS_ZERO_SHADOW", "auto")
         self.wire_shadows = True if self.defer else ((self.ws <= 2) if sh == "auto" else (sh == "wire"))
@@ -145,7 +151,8 @@ class BucketFusedAdamW:
         self._gather_pending = False
         self._gather_event = None
         if self.defer:
-            ddp.register_forward_pre_hook(lambda _m, _a: self.launch_param_gather())
+            if not self.lazy:
+                ddp.register_forward_pre_hook(lambda _m, _a: self.launch_param_gather())
             ddp.module.register_state_dict_pre_hook(lambda *_a, **_k: self.sync_params())
         self.hyper = torch.zeros(8, dtype=torch.float32, device=dev)
         self._hyper_host = torch.zeros(16, 8, dtype=torch.float32).pin_memory()
@@ -228,7 +235,7 @@ class BucketFusedAdamW:
                 self.garena.peer_ptrs_c, self.parena.peer_ptrs_c, self.sarena.peer_ptrs_c if self.wire_shadows else None,
                 self.garena.signal_ptrs_c, self._mc, ctypes.c_longlong(boff), ctypes.c_longlong(numel), _native.p(m),
                 _native.p(v), _native.p(self.hyper), _native.p(self.step_dev), ctypes.c_int(self.mode),
-                ctypes.c_int(self.rank), ctypes.c_int(self.ws), ctypes.c_int(0), ctypes.c_int(0),
+                ctypes.c_int(self.rank), ctypes.c_int(self.ws), ctypes.c_int(self.blocks), ctypes.c_int(0),
                 ctypes.c_int(self.variant), ctypes.c_int(int(self._defer_bucket[bi])), ctypes.c_int(self._eager[bi][0]),
                 self._eager[bi][1], self._eager[bi][2], ctypes.c_void_p(red.stream.cuda_stream)), "zero_adamw_bucket")
             if not self.wire_shadows:

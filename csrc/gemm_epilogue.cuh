@@ -220,7 +220,9 @@ __device__ __forceinline__ void swiglu_bwd_chunk(const Params& p, int row, int c
 
 // epilogue warps per CTA: the optimizer epilogue streams 26 bytes per accumulator element and needs twice the loads
 // in flight of a plain store epilogue
-template <int EPI> struct EpiWarps { static constexpr int N = EPI == EPI_ADAMW ? 8 : 4; };
+// (the SwiGLU-backward epilogue has two dependent 16-byte loads per 8 elements on its critical path: with 4 warps the
+// dgrad GEMM ran at 35 % tensor-pipe activity — ncu, profiles/r2/ncu_r2_summary.md — i.e. epilogue-bound)
+template <int EPI> struct EpiWarps { static constexpr int N = (EPI == EPI_ADAMW || EPI == EPI_SWIGLU_BWD) ? 8 : 4; };
 
 template <int EPI>
 __device__ __forceinline__ void store_chunk(const Params& p, int row, int col0, const uint32_t (&r)[32]) {

@@ -193,95 +193,146 @@ __global__ void __launch_bounds__(128) rmsnorm_bwd_dx_kernel(const TDY* __restri
   }
 }
 
-// dx AND the dw partial sums in one pass (the split above re-reads dy and x for dw: +20 MB and one more launch per
-// norm).  Persistent: gridDim.x CTAs of 128 threads walk the rows with stride gridDim.x; the NEXT row's dy, x and
-// incoming residual gradient are already in flight (second register set) while the current row is reduced and
-// written, and the gain vector w stays in registers for the whole kernel.  Each thread owns VPT float4 columns and
-// accumulates dw for them over its rows; partial[blockIdx.x][:] is reduced by colsum4_kernel afterwards.
-template <typename TDY, int VPT>
-struct RowRegs {
-  f32x4 g[VPT], xv[VPT], dr[VPT];
+// dx AND the dw partial sums in one pass, one WARP per row (the split above re-reads dy and x for dw: +20 MB and one
+// more launch per norm; a persistent CTA-per-row loop with block-wide reductions measured 23 us per call, its
+// iteration time pinned to the memory latency).  A warp holds its row's dy and x in registers (NV float4 columns per
+// lane), reduces dy·w·x with shuffles — no block barrier anywhere in the row loop — and writes dx; eight warps per
+// CTA and two CTAs per SM keep ~200 KB of loads in flight per SM.  Each warp accumulates its rows' dy·x·rstd into its
+// OWN d-wide slot of shared memory (no atomics); the CTA's eight slots are summed into partial[blockIdx.x][:] at the
+// end and colsum_rows_kernel reduces the partial matrix.
+// the row's dy stays in its storage format (4 bf16 = 2 registers) and is widened where it is used
+template <typename TDY> struct DyPack;
+template <> struct DyPack<__nv_bfloat16> {
+  uint2 raw;
+  __device__ __forceinline__ void load(const __nv_bfloat16* p, size_t off) { raw = *reinterpret_cast<const uint2*>(p + off); }
+  __device__ __forceinline__ f32x4 get() const {
+    const float2 a = unpack_bf16x2(raw.x), b = unpack_bf16x2(raw.y);
+    return f32x4{a.x, a.y, b.x, b.y};
+  }
 };
-template <typename TDY, int VPT>
-__device__ __forceinline__ void rms_load_row(RowRegs<TDY, VPT>& R, const TDY* __restrict__ dy, const float* __restrict__ x,
-                                             const float* __restrict__ dres_in, int r, int d, int nvec) {
-  const size_t base = (size_t)r * d;
-#pragma unroll
-  for (int v = 0; v < VPT; ++v) {
-    const int c = threadIdx.x + 128 * v;
-    if (c < nvec) {
-      R.g[v] = ld_dy4<TDY>(dy, base + 4 * c);
-      R.xv[v] = *reinterpret_cast<const f32x4*>(x + base + 4 * c);
-      if (dres_in) R.dr[v] = *reinterpret_cast<const f32x4*>(dres_in + base + 4 * c);
-    }
-  }
-}
-template <typename TDY, int VPT>
-__device__ __forceinline__ void rms_process_row(RowRegs<TDY, VPT>& R, const f32x4 (&wv)[VPT], f32x4 (&acc)[VPT], float rs,
-                                                const float* __restrict__ dres_in, float* __restrict__ dx,
-                                                __nv_bfloat16* __restrict__ dx_bf16, int r, int d, int nvec, float* red) {
-  const size_t base = (size_t)r * d;
-  float dot = 0.f;
-#pragma unroll
-  for (int v = 0; v < VPT; ++v) {
-    const int c = threadIdx.x + 128 * v;
-    if (c < nvec) {
-      f32x4& g = R.g[v];
-      const f32x4& xv = R.xv[v];
-      acc[v].x += g.x * xv.x * rs; acc[v].y += g.y * xv.y * rs; acc[v].z += g.z * xv.z * rs; acc[v].w += g.w * xv.w * rs;
-      g.x *= wv[v].x; g.y *= wv[v].y; g.z *= wv[v].z; g.w *= wv[v].w;
-      dot += g.x * xv.x + g.y * xv.y + g.z * xv.z + g.w * xv.w;
-    }
-  }
-  dot = block_sum(dot, red) * rs / (float)d;  // mean(g * xhat)
-  const float k2 = rs * rs * dot;
-#pragma unroll
-  for (int v = 0; v < VPT; ++v) {
-    const int c = threadIdx.x + 128 * v;
-    if (c < nvec) {
-      const f32x4& g = R.g[v];
-      const f32x4& xv = R.xv[v];
-      f32x4 o{rs * g.x - k2 * xv.x, rs * g.y - k2 * xv.y, rs * g.z - k2 * xv.z, rs * g.w - k2 * xv.w};
-      if (dres_in) { o.x += R.dr[v].x; o.y += R.dr[v].y; o.z += R.dr[v].z; o.w += R.dr[v].w; }
-      if (dx) *reinterpret_cast<f32x4*>(dx + base + 4 * c) = o;
-      if (dx_bf16) *reinterpret_cast<uint2*>(dx_bf16 + base + 4 * c) = uint2{pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w)};
-    }
-  }
-}
-template <typename TDY, int VPT>
-__global__ void __launch_bounds__(128) rmsnorm_bwd_fused_kernel(const TDY* __restrict__ dy, const float* __restrict__ x,
-                                                                const float* __restrict__ w, const float* __restrict__ rstd,
-                                                                const float* __restrict__ dres_in, float* __restrict__ dx,
-                                                                __nv_bfloat16* __restrict__ dx_bf16,
-                                                                float* __restrict__ partial, int T, int d) {
-  __shared__ float red[32];
+template <> struct DyPack<float> {
+  f32x4 raw;
+  __device__ __forceinline__ void load(const float* p, size_t off) { raw = *reinterpret_cast<const f32x4*>(p + off); }
+  __device__ __forceinline__ f32x4 get() const { return raw; }
+};
+
+template <typename TDY, int NV>
+__global__ void __launch_bounds__(256, (NV * (4 + (int)sizeof(TDY)) <= 13 * 6) ? 2 : 1)
+rmsnorm_bwd_rows_kernel(const TDY* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ w,
+                        const float* __restrict__ rstd, const float* __restrict__ dres_in, float* __restrict__ dx,
+                        __nv_bfloat16* __restrict__ dx_bf16, float* __restrict__ partial, int T, int d) {
+  extern __shared__ float sacc[];  // [8 warps][d] dw slots, then [d] gains
   ptx::griddep_launch();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nvec = d >> 2;
-  const int G = gridDim.x;
-  f32x4 wv[VPT], acc[VPT];
-#pragma unroll
-  for (int v = 0; v < VPT; ++v) {
-    const int c = threadIdx.x + 128 * v;
-    acc[v] = f32x4{0.f, 0.f, 0.f, 0.f};
-    wv[v] = c < nvec ? *reinterpret_cast<const f32x4*>(w + 4 * c) : f32x4{0.f, 0.f, 0.f, 0.f};  // parameters: not produced by the previous kernel
-  }
+  float* mine = sacc + (size_t)warp * d;
+  float* sw = sacc + (size_t)8 * d;
+  // the gain vector is a parameter (not produced by the previous kernel): stage it before the dependency wait
+  for (int c = threadIdx.x; c < nvec; c += 256) *reinterpret_cast<f32x4*>(sw + 4 * c) = *reinterpret_cast<const f32x4*>(w + 4 * c);
+  __syncthreads();
   ptx::griddep_wait();
-  RowRegs<TDY, VPT> A, B;
-  int r = blockIdx.x;
-  if (r < T) rms_load_row<TDY, VPT>(A, dy, x, dres_in, r, d, nvec);
-  while (r < T) {
-    if (r + G < T) rms_load_row<TDY, VPT>(B, dy, x, dres_in, r + G, d, nvec);
-    rms_process_row<TDY, VPT>(A, wv, acc, rstd[r], dres_in, dx, dx_bf16, r, d, nvec, red);
-    r += G;
-    if (r >= T) break;
-    if (r + G < T) rms_load_row<TDY, VPT>(A, dy, x, dres_in, r + G, d, nvec);
-    rms_process_row<TDY, VPT>(B, wv, acc, rstd[r], dres_in, dx, dx_bf16, r, d, nvec, red);
-    r += G;
-  }
+  bool first = true;
+  for (int r = blockIdx.x * 8 + warp; r < T; r += gridDim.x * 8) {
+    const size_t base = (size_t)r * d;
+    const float rs = rstd[r];
+    if (dres_in) {  // needed last: pull the row towards L2 now, without tying up registers
 #pragma unroll
-  for (int v = 0; v < VPT; ++v) {
-    const int c = threadIdx.x + 128 * v;
-    if (c < nvec) *reinterpret_cast<f32x4*>(partial + (size_t)blockIdx.x * d + 4 * c) = acc[v];
+      for (int i = 0; i < NV; ++i) {
+        const int c = lane + 32 * i;
+        if (c < nvec && (c & 7) == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(dres_in + base + 4 * c));
+      }
+    }
+    DyPack<TDY> gy[NV];
+    f32x4 xv[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nvec) {
+        gy[i].load(dy, base + 4 * c);
+        xv[i] = *reinterpret_cast<const f32x4*>(x + base + 4 * c);
+      }
+    }
+    float dot = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nvec) {
+        const f32x4 g = gy[i].get();
+        // this row's contribution to dw (raw dy), into the warp's own shared-memory slot
+        const f32x4 a{g.x * xv[i].x * rs, g.y * xv[i].y * rs, g.z * xv[i].z * rs, g.w * xv[i].w * rs};
+        f32x4* slot = reinterpret_cast<f32x4*>(mine + 4 * c);
+        if (first) {
+          *slot = a;
+        } else {
+          const f32x4 o = *slot;
+          *slot = f32x4{o.x + a.x, o.y + a.y, o.z + a.z, o.w + a.w};
+        }
+        const f32x4 wv = *reinterpret_cast<const f32x4*>(sw + 4 * c);
+        dot += g.x * wv.x * xv[i].x + g.y * wv.y * xv[i].y + g.z * wv.z * xv[i].z + g.w * wv.w * xv[i].w;
+      }
+    }
+    first = false;
+    dot = warp_sum(dot) * rs / (float)d;  // mean(dy*w * xhat)
+    const float k2 = rs * rs * dot;       // rs*(g - xhat*dot) = rs*g - rs^2*dot*x
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nvec) {
+        const f32x4 g = gy[i].get();
+        const f32x4 wv = *reinterpret_cast<const f32x4*>(sw + 4 * c);
+        f32x4 o{rs * g.x * wv.x - k2 * xv[i].x, rs * g.y * wv.y - k2 * xv[i].y, rs * g.z * wv.z - k2 * xv[i].z,
+                rs * g.w * wv.w - k2 * xv[i].w};
+        if (dres_in) {
+          const f32x4 dr = *reinterpret_cast<const f32x4*>(dres_in + base + 4 * c);
+          o.x += dr.x; o.y += dr.y; o.z += dr.z; o.w += dr.w;
+        }
+        if (dx) *reinterpret_cast<f32x4*>(dx + base + 4 * c) = o;
+        if (dx_bf16) *reinterpret_cast<uint2*>(dx_bf16 + base + 4 * c) = uint2{pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w)};
+      }
+    }
+  }
+  if (first) {  // this warp had no row: its slot must still read as zero
+    for (int c = lane; c < nvec; c += 32) *reinterpret_cast<f32x4*>(mine + 4 * c) = f32x4{0.f, 0.f, 0.f, 0.f};
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < nvec; c += 256) {
+    f32x4 t = *reinterpret_cast<const f32x4*>(sacc + 4 * c);
+#pragma unroll
+    for (int ww = 1; ww < 8; ++ww) {
+      const f32x4 u = *reinterpret_cast<const f32x4*>(sacc + (size_t)ww * d + 4 * c);
+      t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
+    }
+    *reinterpret_cast<f32x4*>(partial + (size_t)blockIdx.x * d + 4 * c) = t;
+  }
+}
+
+// column sums of a [rows, d] partial matrix: 32 columns x 8 row groups per CTA (coalesced 128-byte row segments,
+// rows/8 independent loads per thread), combined through shared memory.  d/32 CTAs.
+__global__ void __launch_bounds__(256) colsum_rows_kernel(const float* __restrict__ partial, float* __restrict__ out,
+                                                          int rows, int d, int accumulate) {
+  __shared__ float red[8][33];
+  ptx::griddep_launch();
+  ptx::griddep_wait();
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int j = blockIdx.x * 32 + tx;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  if (j < d) {
+    int r = ty;
+    for (; r + 24 < rows; r += 32) {
+      s0 += partial[(size_t)r * d + j];
+      s1 += partial[(size_t)(r + 8) * d + j];
+      s2 += partial[(size_t)(r + 16) * d + j];
+      s3 += partial[(size_t)(r + 24) * d + j];
+    }
+    for (; r < rows; r += 8) s0 += partial[(size_t)r * d + j];
+  }
+  red[ty][tx] = (s0 + s1) + (s2 + s3);
+  __syncthreads();
+  if (ty == 0 && j < d) {
+    float s = 0.f;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) s += red[q][tx];
+    out[j] = accumulate ? out[j] + s : s;
   }
 }
 
@@ -403,23 +454,33 @@ extern "C" int b200_rmsnorm_bwd(const void* dy, int dy_dtype, const float* x, co
       const char* e = getenv("B200SYS_RMSNORM_BWD");
       fused_mode = (e && e[0] == 's') ? 0 : 1;  // "split": the two-kernel form (A/B measurements)
     }
-    if (fused_mode && d <= 128 * 4 * 6) {
-      // one pass: dx + per-CTA dw partials (grid = workspace rows, so the scratch contract holds), then the column sum
-#define LAUNCH_F(TDY, VPL)                                                                                         \
-  B200_CHECK_CUDA(launch_pdl(rmsnorm_bwd_fused_kernel<TDY, VPL>, dim3(grid), dim3(128), 0, s,                       \
-                             reinterpret_cast<const TDY*>(dy), x, w, rstd, dres_in, dx, dxb, scratch, T, d))
-#define BY_DT_F(VPL)                                                   \
-  do {                                                                 \
-    if (dy_dtype == B200_BF16) LAUNCH_F(__nv_bfloat16, VPL);           \
-    else LAUNCH_F(float, VPL);                                         \
+    const int nv = ceil_div(d >> 2, 32);
+    if (fused_mode && nv <= 24) {
+      // one pass: dx + per-CTA dw partials (<= workspace rows CTAs, so the scratch contract holds), then the column sum
+      const int fgrid = std::min(grid, ceil_div(T, 8));
+      const size_t smem = (size_t)9 * d * sizeof(float);
+#define LAUNCH_R(TDY, NVV)                                                                                          \
+  do {                                                                                                              \
+    auto kfn = rmsnorm_bwd_rows_kernel<TDY, NVV>;                                                                   \
+    B200_ENSURE_DYN_SMEM(kfn, 9 * 4 * 128 * NVV);                                                                   \
+    B200_CHECK_CUDA(launch_pdl(kfn, dim3(fgrid), dim3(256), smem, s, reinterpret_cast<const TDY*>(dy), x, w, rstd,  \
+                               dres_in, dx, dxb, scratch, T, d));                                                   \
   } while (0)
-      if (d <= 512 * 2) BY_DT_F(2);
-      else if (d <= 512 * 4) BY_DT_F(4);
-      else BY_DT_F(6);
-#undef BY_DT_F
-#undef LAUNCH_F
-      B200_CHECK_CUDA(launch_pdl(colsum4_kernel, dim3(ceil_div(d, 64)), dim3(256), 0, s, (const float*)scratch, dw, grid, d,
-                                 dw_accumulate));
+#define BY_DT_R(NVV)                                                   \
+  do {                                                                 \
+    if (dy_dtype == B200_BF16) LAUNCH_R(__nv_bfloat16, NVV);           \
+    else LAUNCH_R(float, NVV);                                         \
+  } while (0)
+      if (nv <= 4) BY_DT_R(4);
+      else if (nv <= 8) BY_DT_R(8);
+      else if (nv <= 13) BY_DT_R(13);
+      else if (nv <= 16) BY_DT_R(16);
+      else if (nv <= 20) BY_DT_R(20);
+      else BY_DT_R(24);
+#undef BY_DT_R
+#undef LAUNCH_R
+      B200_CHECK_CUDA(launch_pdl(colsum_rows_kernel, dim3(ceil_div(d, 32)), dim3(256), 0, s, (const float*)scratch, dw,
+                                 fgrid, d, dw_accumulate));
       return 0;
     }
     // fast path; the dw partial matrix has `chunks` <= workspace rows, so the scratch contract holds

@@ -171,13 +171,15 @@ def _zero_variants_worker(rank, ws, port):
     ref, ref_losses = run(lambda m: AdamW(m.parameters(), lr=1e-3, weight_decay=0.1), False, 8)
     refp = dict(ref.module.named_parameters())
     have_mc = bool(ref._reducer.arena.multicast_ptr)
-    for variant in ([0, 1, 2, 3] if have_mc else [0]):
-        for defer in (False, True):
+    variants = [0, 1, 2, 3] if have_mc else [0]
+    for variant in variants:
+        # "lazy" (fp32 replicas refreshed only by sync_params) once, on the default kernel of large jobs
+        for defer in ((False, True, "lazy") if variant == variants[-1] else (False, True)):
             for graph in (False, True):
                 def make(m, variant=variant, defer=defer):
                     o = ShardedOptimizer(m.parameters(), AdamW, lr=1e-3, weight_decay=0.1)
                     assert o.enable_symmetric(m, defer_fp32_gather=defer, variant=variant)
-                    assert o._symm.variant == variant and o._symm.defer == defer
+                    assert o._symm.variant == variant and o._symm.defer == bool(defer) and o._symm.lazy == (defer == "lazy")
                     return o
                 m, losses = run(make, graph, 8)
                 tag = f"variant {variant} defer {defer} graph {graph}"

@@ -26,10 +26,10 @@ if "gemm" in which:
         k.wgrad(dy2, x1, out=out2)                               # wgrad TN 12800x1600x2048
     # optimizer in the wgrad epilogue (EPI_ADAMW)
     pm = [torch.randn(2 * dff, d, device=dev) * 0.02, torch.zeros(2 * dff, d, device=dev), torch.zeros(2 * dff, d, device=dev)]
-    dh = k.DeviceHyper(dev, 1); dh.set(1e-4, 0.9, 0.95, 1e-8, 0.1)
+    dhy = k.DeviceHyper(dev, 1); dhy.set(1e-4, 0.9, 0.95, 1e-8, 0.1)
     sh = torch.empty(2 * dff, d, device=dev, dtype=torch.bfloat16)
     for _ in range(reps):
-        k.wgrad_adamw(dy2, x1, [pm[0]], [pm[1]], [pm[2]], sh, dh)
+        k.wgrad_adamw(dy2, x1, [pm[0]], [pm[1]], [pm[2]], sh, dhy)
 if "pair" in which:
     # CTA-pair (cta_group::2) kernel, forced: fwd NT 2048x12800x1600 (w1|w3) and dgrad NN 2048x1600x12800
     x, w13 = bf(T, d), bf(2 * dff, d) * 0.05
