@@ -130,14 +130,75 @@ def bench_wgrad_adamw(M: int, N: int, K: int, iters: int = 20):
     return _graph_time(fused, iters), _graph_time(sep, iters)
 
 
+def tune(model: str, tokens: int, out_path: str):
+    """Time every legal (kernel, tile width) per LM shape and write the winners to ``ops/gemm_tuned.json``."""
+    plans, report = {}, []
+    for name, kind, M, N, K in lm_shapes(model, tokens):
+        if kind == "tn":
+            # wgrads run as the transpose: A = x [K, N] (MN-major), B = dy [K, M] (MN-major), C^T [N, M]
+            gm, gn, a_mn, b_mn = N, M, True, True
+            mk = lambda bn, pair: (lambda a, b, out: kernels.gemm(b, a, a_mn=True, b_mn=True, epilogue=kernels.EPI_F32_T, out=out, force_bn=bn, pair=pair))
+        elif kind == "nn":
+            gm, gn, a_mn, b_mn = M, N, False, True
+            mk = lambda bn, pair: (lambda a, b, out: kernels.gemm(a, b, b_mn=True, out=out, force_bn=bn, pair=pair))
+        else:
+            gm, gn, a_mn, b_mn = M, N, False, False
+            mk = lambda bn, pair: (lambda a, b, out: kernels.gemm(a, b, out=out, force_bn=bn, pair=pair))
+        dev = "cuda"
+        sets = []
+        for _ in range(4):
+            if kind == "nt":
+                sets.append((torch.randn(M, K, device=dev).bfloat16(), torch.randn(N, K, device=dev).bfloat16(),
+                             torch.empty(M, N, device=dev, dtype=torch.bfloat16)))
+            elif kind == "nn":
+                sets.append((torch.randn(M, K, device=dev).bfloat16(), torch.randn(K, N, device=dev).bfloat16(),
+                             torch.empty(M, N, device=dev, dtype=torch.bfloat16)))
+            else:
+                sets.append((torch.randn(K, M, device=dev).bfloat16(), torch.randn(K, N, device=dev).bfloat16(),
+                             torch.empty(M, N, device=dev)))
+        best = None
+        for pair in (False, True):
+            if pair and gm < 256:
+                continue
+            for bn in (128, 192, 256):
+                if pair and b_mn and bn == 192:
+                    continue
+                fn = mk(bn, pair)
+                try:
+                    t = _graph_time([lambda s_=s_: fn(*s_) for s_ in sets], 10)
+                except Exception as e:  # illegal combination for this layout
+                    report.append(f"{name} pair={pair} bn={bn}: {type(e).__name__}")
+                    continue
+                report.append(f"{name} pair={int(pair)} bn={bn}: {1e3 * t:.1f} us")
+                if best is None or t < best[0]:
+                    best = (t, pair, bn)
+        plans[f"{gm},{gn},{K},{int(a_mn)},{int(b_mn)}"] = [int(best[1]), best[2]]
+        print(f"{name:12s} -> pair={int(best[1])} bn={best[2]} ({1e3 * best[0]:.1f} us)", flush=True)
+    try:
+        old = json.load(open(out_path)).get("plans", {})
+    except Exception:
+        old = {}
+    old.update(plans)
+    json.dump({"note": "measured on B200 by bench/gemm.py --tune: key = M,N,K,a_mn,b_mn of the GEMM as launched "
+                       "(wgrads as their transpose); value = [CTA-pair kernel, tile width]", "plans": old},
+              open(out_path, "w"), indent=1, sort_keys=True)
+    return report
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--tune", action="store_true", help="time every kernel x tile width per shape, write ops/gemm_tuned.json")
     ap.add_argument("--model", default="xl")
     ap.add_argument("--tokens", type=int, default=2048)
     ap.add_argument("--bn", type=int, default=0)
     ap.add_argument("--pair", choices=["auto", "0", "1"], default="auto", help="CTA-pair (cta_group::2) kernel: planner / never / always")
     ap.add_argument("--json", default=None)
     args = ap.parse_args()
+    if args.tune:
+        path = os.path.join(os.path.dirname(__file__), "..", "ops", "gemm_tuned.json")
+        for line in tune(args.model, args.tokens, os.path.abspath(path)):
+            print(line)
+        return
     from ..utils.clocks import ClockSampler
     peak = peak_tflops()
     pair = None if args.pair == "auto" else args.pair == "1"

@@ -133,8 +133,10 @@ class SwiGLU(nn.Module):
             if not torch.is_grad_enabled():  # serving / eval: the gate runs in the GEMM epilogue
                 h = native.swiglu_linear_nograd(x, self.w1.weight, self.w3.weight)
                 return native.linear(h, (self.w2.weight,))
-            if os.environ.get("B200SYS_FUSE_SWIGLU", "1") == "1":
-                y = native.swiglu_ffn(x, self.w1.weight, self.w3.weight, self.w2.weight)  # gate in the GEMM epilogues
+            mode = os.environ.get("B200SYS_FUSE_SWIGLU", "1")  # 0: separate gate kernels, 1: forward epilogue, 2: both
+            if mode != "0":
+                native.SwiGLUFFNFn.FUSE_BACKWARD = mode == "2"
+                y = native.swiglu_ffn(x, self.w1.weight, self.w3.weight, self.w2.weight)  # gate in the GEMM epilogue(s)
                 if y is not None:
                     return y
             ab = native.linear(x, (self.w1.weight, self.w3.weight))  # one GEMM → [.., 2*d_ff]

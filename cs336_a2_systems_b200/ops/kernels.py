@@ -62,6 +62,30 @@ def _lib():
 import functools as _functools
 
 
+def _load_tuned() -> dict:
+    """Measured plans: ``ops/gemm_tuned.json`` maps "M,N,K,a_mn,b_mn" to [use_pair, tile width], written by
+    ``python -m cs336_a2_systems_b200.bench.gemm --tune`` on a B200 (every legal kernel x tile width timed per shape).
+    Shapes that are not in the table fall back to the wave model below."""
+    import json as _json
+    import os as _os
+    try:
+        with open(_os.path.join(_os.path.dirname(__file__), "gemm_tuned.json")) as f:
+            return {k: (bool(v[0]), int(v[1])) for k, v in _json.load(f).get("plans", {}).items()}
+    except Exception:
+        return {}
+
+
+_TUNED = _load_tuned() if _environ.get("B200SYS_GEMM_TUNED", "1") == "1" else {}
+
+
+def plan_gemm(M: int, N: int, K: int, a_mn: bool, b_mn: bool, pair_ok: bool):
+    """(use_pair, tile width) for C[M, N] = A·Bᵀ: the measured plan for this exact shape if there is one, else the model."""
+    t = _TUNED.get(f"{M},{N},{K},{int(a_mn)},{int(b_mn)}")
+    if t is not None and (pair_ok or not t[0]):
+        return t
+    return _plan_gemm(M, N, b_mn, pair_ok)
+
+
 @_functools.lru_cache(maxsize=None)
 def _plan_gemm(M: int, N: int, b_mn: bool, pair_ok: bool, sms: int = 148):
     """Pick (use_pair, tile width) by a wave model calibrated on B200 (profiles/gemm_*): a 1-CTA tile of width BN
@@ -142,7 +166,7 @@ def gemm(a: Tensor, b: Tensor, *, a_mn: bool = False, b_mn: bool = False, epilog
     # CTA-pair kernel (tcgen05 cta_group::2, 256-row tiles): plain / fp32 / RoPE / transposed epilogues
     pair_ok = epilogue in (EPI_BF16, EPI_F32, EPI_BF16_ROPE, EPI_F32_T) and not (a_mn and not b_mn) and M >= 256
     if pair is None and GEMM_PAIR == "auto" and force_bn == 0:
-        use_pair, force_bn = _plan_gemm(M, N, b_mn, pair_ok)
+        use_pair, force_bn = plan_gemm(M, N, K, a_mn, b_mn, pair_ok)
     else:
         use_pair = pair_ok and (pair if pair is not None else GEMM_PAIR == "1")
     fn = _lib().b200_gemm2_bf16_ex if use_pair else _lib().b200_gemm_bf16_ex

@@ -336,6 +336,11 @@ class SwiGLUFFNFn(torch.autograd.Function):
 
     Saved for backward: ``x``, ``ab``, ``g`` and the two weight shadows — what the unfused chain saves too."""
 
+    #: apply the gate's backward inside the w2 dgrad GEMM (True) or as the separate elementwise kernel (False).
+    #: Measured on B200 (profiles/r2): the forward fusion saves ~7 us per layer; the backward epilogue (two dependent
+    #: 16-byte loads per 8 elements) makes the dgrad GEMM epilogue-bound and loses more than the saved kernel costs.
+    FUSE_BACKWARD = False
+
     @staticmethod
     def forward(ctx, x: Tensor, wb13: Tensor, wb2: Tensor, w1: Tensor, w3: Tensor, w2: Tensor):
         K = wb13.shape[1]
@@ -353,7 +358,10 @@ class SwiGLUFFNFn(torch.autograd.Function):
         w1, w3, w2 = ctx.weights
         dy2 = _to_bf16_2d(dy, wb2.shape[0])
         need = ctx.needs_input_grad
-        dab = kernels.gemm_swiglu_bwd(dy2, wb2, ab)
+        if SwiGLUFFNFn.FUSE_BACKWARD:
+            dab = kernels.gemm_swiglu_bwd(dy2, wb2, ab)
+        else:
+            dab = kernels.swiglu_bwd(ab, kernels.gemm(dy2, wb2, b_mn=True))
         dx = None
         if need[0]:
             dx = kernels.gemm(dab, wb13, b_mn=True).view(ctx.x_shape)

@@ -751,43 +751,85 @@ fa2_bwd_wgr_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   }
 }
 
-// delta[b,h,i] = sum_d O[b,h,i,d] * dO[b,h,i,d]; one warp per row.  O / dO are bf16 or fp32 (o_f32 / do_f32); with
+// delta[b,h,i] = sum_d O[b,h,i,d] * dO[b,h,i,d].  TPR threads per row (a power of two >= D/8), 8 elements = one or two
+// 16-byte loads per thread and operand, a TPR-wide shuffle reduction: 32/TPR rows per warp (the first version spent a
+// whole warp and 2-element loads on a 64-element row: 17 us for 13 MB).  O / dO are bf16 or fp32 (o_f32 / do_f32); with
 // dout_bf16 != nullptr the fp32 dO row is also written out as bf16 in the same pass (contiguous [rows, D]) — the MMA
 // operand of the main kernel — so fp32 callers need no separate cast kernel.
-__global__ void fa2_delta_kernel(const void* __restrict__ o, const void* __restrict__ dout, float* __restrict__ delta,
-                                 int H, int Nq, int D, long long o_sb, long long o_sh, long long o_sr, long long d_sb,
-                                 long long d_sh, long long d_sr, long long rows, int o_f32, int do_f32,
-                                 __nv_bfloat16* __restrict__ dout_bf16) {
+template <int TPR>
+__global__ void __launch_bounds__(256) fa2_delta_kernel(const void* __restrict__ o, const void* __restrict__ dout,
+                                                        float* __restrict__ delta, int H, int Nq, int D, long long o_sb,
+                                                        long long o_sh, long long o_sr, long long d_sb, long long d_sh,
+                                                        long long d_sr, long long rows, int o_f32, int do_f32,
+                                                        __nv_bfloat16* __restrict__ dout_bf16) {
   ptx::griddep_launch();
   ptx::griddep_wait();
-  const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (w >= rows) return;
-  const int i = (int)(w % Nq);
-  const long long bh = w / Nq;
-  const int hh = (int)(bh % H);
-  const long long bb = bh / H;
-  const long long o_off = bb * o_sb + hh * o_sh + (long long)i * o_sr;
-  const long long d_off = bb * d_sb + hh * d_sh + (long long)i * d_sr;
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long w = t / TPR;          // row
+  const int sub = (int)(t % TPR);       // 8-element group inside the row
+  const int d = sub * 8;
   float acc = 0.f;
-  for (int d = lane * 2; d < D; d += 64) {
-    float2 a, g;
-    if (o_f32) a = *reinterpret_cast<const float2*>(reinterpret_cast<const float*>(o) + o_off + d);
-    else a = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(reinterpret_cast<const __nv_bfloat16*>(o) + o_off + d));
+  if (w < rows && d < D) {
+    const unsigned rows_per_b = (unsigned)H * (unsigned)Nq;
+    const long long bb = w / rows_per_b;
+    const unsigned rem = (unsigned)(w - bb * rows_per_b);
+    const unsigned hh = rem / (unsigned)Nq, i = rem - hh * (unsigned)Nq;
+    const long long o_off = bb * o_sb + (long long)hh * o_sh + (long long)i * o_sr + d;
+    const long long d_off = bb * d_sb + (long long)hh * d_sh + (long long)i * d_sr + d;
+    float a[8], g[8];
+    if (o_f32) {
+      const float* p = reinterpret_cast<const float*>(o) + o_off;
+      if ((reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+        const f32x4 u = *reinterpret_cast<const f32x4*>(p), v = *reinterpret_cast<const f32x4*>(p + 4);
+        a[0] = u.x; a[1] = u.y; a[2] = u.z; a[3] = u.w; a[4] = v.x; a[5] = v.y; a[6] = v.z; a[7] = v.w;
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) a[e] = p[e];
+      }
+    } else {
+      const __nv_bfloat16* p = reinterpret_cast<const __nv_bfloat16*>(o) + o_off;
+      if ((reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+        const u32x4 u = *reinterpret_cast<const u32x4*>(p);
+        const uint32_t ww[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) { const float2 f = unpack_bf16x2(ww[e]); a[2 * e] = f.x; a[2 * e + 1] = f.y; }
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) a[e] = __bfloat162float(p[e]);
+      }
+    }
     if (do_f32) {
-      g = *reinterpret_cast<const float2*>(reinterpret_cast<const float*>(dout) + d_off + d);
+      const float* p = reinterpret_cast<const float*>(dout) + d_off;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) g[e] = p[e];
       // delta must see the SAME rounding of dO as the dP = dO·Vᵀ MMA does, or P∘(dP − delta) stops cancelling where it
       // should be exactly zero (a causal row that attends to one key only)
-      const uint32_t gb = pack_bf16x2(g.x, g.y);
-      g = unpack_bf16x2(gb);
-      if (dout_bf16) *reinterpret_cast<uint32_t*>(dout_bf16 + w * D + d) = gb;
+      uint32_t gb[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        gb[e] = pack_bf16x2(g[2 * e], g[2 * e + 1]);
+        const float2 f = unpack_bf16x2(gb[e]);
+        g[2 * e] = f.x; g[2 * e + 1] = f.y;
+      }
+      if (dout_bf16) *reinterpret_cast<u32x4*>(dout_bf16 + w * D + d) = u32x4{gb[0], gb[1], gb[2], gb[3]};
     } else {
-      g = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(reinterpret_cast<const __nv_bfloat16*>(dout) + d_off + d));
+      const __nv_bfloat16* p = reinterpret_cast<const __nv_bfloat16*>(dout) + d_off;
+      if ((reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+        const u32x4 u = *reinterpret_cast<const u32x4*>(p);
+        const uint32_t ww[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) { const float2 f = unpack_bf16x2(ww[e]); g[2 * e] = f.x; g[2 * e + 1] = f.y; }
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) g[e] = __bfloat162float(p[e]);
+      }
     }
-    acc += a.x * g.x + a.y * g.y;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc += a[e] * g[e];
   }
-  acc = warp_sum(acc);
-  if (lane == 0) delta[w] = acc;
+#pragma unroll
+  for (int off = TPR / 2; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+  if (sub == 0 && w < rows) delta[w] = acc;
 }
 
 // 8 consecutive elements of one row per thread (D is a multiple of 8): two 16-byte loads, one 16- or 32-byte store,
@@ -916,10 +958,16 @@ extern "C" int b200_fa2_bwd_ex(const void* q, const void* k, const void* v, cons
   const long long rows = (long long)B * H * Nq;
   {
     const int threads = 256;
-    const long long blocks = (rows * 32 + threads - 1) / threads;
-    B200_CHECK_CUDA(launch_pdl(fa2_delta_kernel, dim3((unsigned)blocks), dim3(threads), 0, s, o, dout, delta, H, Nq, D,
-                               o_strides[0], o_strides[1], o_strides[2], do_strides[0], do_strides[1], do_strides[2],
-                               rows, o_f32, do_f32, reinterpret_cast<__nv_bfloat16*>(do_f32 ? do_bf16_scratch : nullptr)));
+    __nv_bfloat16* scratch = reinterpret_cast<__nv_bfloat16*>(do_f32 ? do_bf16_scratch : nullptr);
+#define LAUNCH_DELTA(TPRV)                                                                                           \
+  B200_CHECK_CUDA(launch_pdl(fa2_delta_kernel<TPRV>, dim3((unsigned)((rows * TPRV + threads - 1) / threads)),         \
+                             dim3(threads), 0, s, o, dout, delta, H, Nq, D, o_strides[0], o_strides[1], o_strides[2], \
+                             do_strides[0], do_strides[1], do_strides[2], rows, o_f32, do_f32, scratch))
+    if (D <= 16) LAUNCH_DELTA(2);
+    else if (D <= 32) LAUNCH_DELTA(4);
+    else if (D <= 64) LAUNCH_DELTA(8);
+    else LAUNCH_DELTA(16);
+#undef LAUNCH_DELTA
   }
   if (!prezeroed) B200_CHECK_CUDA(cudaMemsetAsync(dq_acc, 0, (size_t)rows * D * sizeof(float), s));
   CUtensorMap tq, tk, tv, tdo;

@@ -78,6 +78,62 @@ __global__ void __launch_bounds__(256) rmsnorm_fwd_kernel(const TX* __restrict__
   }
 }
 
+// Warp-per-row forward for the LM's hot case (fp32 residual stream in, bf16 activations out, d % 4 == 0): the row
+// (after the optional residual add) lives in registers — NV float4 columns per lane — the sum of squares is a warp
+// shuffle reduction, no shared memory and no block barrier; eight rows per CTA.  The gain vector is staged in shared
+// memory before the dependency wait (it is a parameter, not an output of the previous kernel).
+template <int NV>
+__global__ void __launch_bounds__(256) rmsnorm_fwd_rows_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ resid,
+                                                               const float* __restrict__ w, __nv_bfloat16* __restrict__ y,
+                                                               float* __restrict__ xout, float* __restrict__ rstd_out,
+                                                               int T, int d, float eps) {
+  extern __shared__ float sw[];
+  ptx::griddep_launch();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nvec = d >> 2;
+  for (int c = threadIdx.x; c < nvec; c += 256) *reinterpret_cast<f32x4*>(sw + 4 * c) = *reinterpret_cast<const f32x4*>(w + 4 * c);
+  __syncthreads();
+  ptx::griddep_wait();
+  for (int r = blockIdx.x * 8 + warp; r < T; r += gridDim.x * 8) {
+    const size_t base = (size_t)r * d;
+    f32x4 v[NV];
+    uint2 rb[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nvec) {
+        v[i] = *reinterpret_cast<const f32x4*>(x + base + 4 * c);
+        if (resid) rb[i] = *reinterpret_cast<const uint2*>(resid + base + 4 * c);
+      }
+    }
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nvec) {
+        if (resid) {
+          const float2 r0 = unpack_bf16x2(rb[i].x), r1 = unpack_bf16x2(rb[i].y);
+          v[i].x += r0.x; v[i].y += r0.y; v[i].z += r1.x; v[i].w += r1.y;
+        }
+        if (xout) *reinterpret_cast<f32x4*>(xout + base + 4 * c) = v[i];
+        ss += v[i].x * v[i].x + v[i].y * v[i].y + v[i].z * v[i].z + v[i].w * v[i].w;
+      }
+    }
+    ss = warp_sum(ss);
+    const float rstd = rsqrtf(ss / (float)d + eps);
+    if (lane == 0 && rstd_out) rstd_out[r] = rstd;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nvec) {
+        const f32x4 wv = *reinterpret_cast<const f32x4*>(sw + 4 * c);
+        *reinterpret_cast<uint2*>(y + base + 4 * c) =
+            uint2{pack_bf16x2(v[i].x * rstd * wv.x, v[i].y * rstd * wv.y), pack_bf16x2(v[i].z * rstd * wv.z, v[i].w * rstd * wv.w)};
+      }
+    }
+  }
+}
+
 // ---- backward --------------------------------------------------------------------------------
 // dx = dres_in + rstd * (g - xhat * mean(g * xhat)),  g = dy * w,  xhat = x * rstd
 // dw[j] = sum_rows dy[r,j] * xhat[r,j]   (per-CTA partials in `dw_partial`, reduced by a 2nd kernel)
@@ -411,6 +467,38 @@ extern "C" int b200_rmsnorm_fwd(const void* x, int x_dtype, const void* resid_bf
   B200_REQUIRE(T > 0 && d > 0, "rmsnorm_fwd: empty input");
   B200_REQUIRE(d * 4 <= 160 * 1024, "rmsnorm_fwd: hidden size %d too large for the smem-staged kernel", d);
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int nv = ceil_div(d >> 2, 32);
+  const bool al16 = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(xout)) & 15) == 0 &&
+                    ((reinterpret_cast<uintptr_t>(resid_bf16) | reinterpret_cast<uintptr_t>(y)) & 7) == 0;
+  if (x_dtype == B200_F32 && y_dtype == B200_BF16 && (d & 3) == 0 && nv <= 24 && al16) {
+    // hot case: one warp per row (getenv B200SYS_RMSNORM_FWD=cta keeps the CTA-per-row kernel for A/B runs)
+    static int rows_mode = -1;
+    if (rows_mode < 0) {
+      const char* e = getenv("B200SYS_RMSNORM_FWD");
+      rows_mode = (e && e[0] == 'c') ? 0 : 1;
+    }
+    if (rows_mode) {
+      const int grid = std::min(ceil_div(T, 8), num_sms() * 4);
+      const size_t sm = (size_t)d * 4;
+#define LAUNCH_FR(NVV)                                                                                               \
+  do {                                                                                                               \
+    auto kfn = rmsnorm_fwd_rows_kernel<NVV>;                                                                         \
+    if (sm > 48 * 1024) B200_ENSURE_DYN_SMEM(kfn, 4 * 128 * NVV);                                                    \
+    B200_CHECK_CUDA(launch_pdl(kfn, dim3(grid), dim3(256), sm, s, reinterpret_cast<const float*>(x),                 \
+                               reinterpret_cast<const __nv_bfloat16*>(resid_bf16), w,                                \
+                               reinterpret_cast<__nv_bfloat16*>(y), xout, rstd, T, d, eps));                         \
+  } while (0)
+      if (nv <= 4) LAUNCH_FR(4);
+      else if (nv <= 8) LAUNCH_FR(8);
+      else if (nv <= 13) LAUNCH_FR(13);
+      else if (nv <= 16) LAUNCH_FR(16);
+      else if (nv <= 20) LAUNCH_FR(20);
+      else LAUNCH_FR(24);
+#undef LAUNCH_FR
+      B200_CHECK_CUDA(cudaGetLastError());
+      return 0;
+    }
+  }
   const int threads = d >= 2048 ? 256 : 128;
   const size_t smem = (size_t)d * 4;
 #define LAUNCH(TX, TY)                                                                                            \

@@ -22,9 +22,7 @@ timeout -s TERM -k 10 200 python -m torch.distributed.run --nnodes=1 --nproc-per
 echo "[zero blocks] rc=$?"
 cell ours_default 200 B200SYS_X=1 --
 cell ours_blocks64 200 B200SYS_ZERO_BLOCKS=64 --
-cell ours_blocks32 200 B200SYS_ZERO_BLOCKS=32 --
 cell ours_lazy 200 B200SYS_X=1 -- --optimizer sharded --defer-gather lazy
-cell ours_bucket10 200 B200SYS_X=1 -- --bucket-mb 10
 cell ours_bucket1000 200 B200SYS_X=1 -- --bucket-mb 1000
 cell ours_27b_sharded 400 B200SYS_X=1 -- --model 2.7b --sharded
 cell reference_27b_sharded 500 B200SYS_X=1 -- --impl reference --model 2.7b --sharded
