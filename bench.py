@@ -67,7 +67,52 @@ def parse_args():
                          "backward (measured slower on B200, see DESIGN.md)")
     ap.add_argument("--no-overlap", action="store_true",
                     help="ours: run the optimizer after backward instead of overlapping it with backward")
+    ap.add_argument("--no-guard", action="store_true",
+                    help="ours, N>1: run in this process instead of as a watched child with fallback configurations "
+                         "(see GUARD_ATTEMPTS); explicit --optimizer/--zero-variant/--comm/... choices imply it")
+    ap.add_argument("--child", action="store_true", help=argparse.SUPPRESS)  # set by the guard for the process it watches
     return ap.parse_args()
+
+
+#: N > 1, default invocation: configurations tried in order by the guard (utils/guard.py).  The first is the product
+#: path; the others exist so that a box on which it stops making progress still yields a measured (and labelled) line.
+GUARD_ATTEMPTS = [
+    ("default", []),
+    ("bucket-fused ZeRO-1 kernel with peer loads/stores instead of NVLS", ["--zero-variant", "0"]),
+    ("NCCL all-reduce per bucket + replicated AdamW", ["--comm", "c10d", "--optimizer", "replicated"]),
+]
+
+
+def _mark(msg: str) -> None:
+    from cs336_a2_systems_b200.utils.guard import heartbeat
+    heartbeat(msg)
+
+
+def guarded_main(args) -> int:
+    """Rank r of the torchrun job becomes the launcher of child rank r (same RANK / LOCAL_RANK / WORLD_SIZE, its own
+    rendezvous port per attempt); rank 0 relays the successful child's JSON line, with the history of attempts."""
+    from cs336_a2_systems_b200 import _native
+    from cs336_a2_systems_b200.utils.guard import run_attempts
+
+    _native.have_lib()  # the launcher maps libb200sys.so too (no CUDA context is created here)
+    rank = int(os.environ.get("RANK", "0"))
+    base = [sys.executable, os.path.abspath(__file__)] + sys.argv[1:] + ["--child"]
+    rc, text, history = run_attempts(base, GUARD_ATTEMPTS, stall_s=float(os.environ.get("B200SYS_GUARD_STALL_S", "75")),
+                                     total_s=float(os.environ.get("B200SYS_GUARD_TOTAL_S", "300")))
+    if rank == 0:
+        all_lines = text.splitlines()
+        idx = [i for i, l in enumerate(all_lines) if l.lstrip().startswith("{")]
+        if rc == 0 and idx:
+            out = json.loads(all_lines[idx[-1]])
+            if len(history) > 1 and isinstance(out.get("config"), dict):
+                out["config"]["guard_attempts"] = history
+            for i, l in enumerate(all_lines):  # anything else the child wrote (library banners) goes first
+                if i != idx[-1] and l.strip():
+                    print(l, flush=True)
+            print(json.dumps(out), flush=True)
+        else:
+            print(json.dumps({"error": "no configuration completed", "impl": "ours", "attempts": history}), flush=True)
+    return rc
 
 
 def init_dist(args):
@@ -140,6 +185,8 @@ def build_ours(args, rank, ws, dev):
         model = DDPIndividualParameters(model, backend=args.comm)
     elif ws > 1:
         model = DDPBucketed(model, bucket_size_mb=args.bucket_mb, backend=args.comm)
+    if ws > 1:
+        _mark(f"DDP wrapper built (gradient backend: {getattr(getattr(model, '_reducer', None), 'kind', '?')})")
     kw = dict(lr=1e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
     fused_sharded = False
     symm_backend = getattr(getattr(model, "_reducer", None), "kind", "") == "symm"
@@ -170,6 +217,8 @@ def build_ours(args, rank, ws, dev):
         if opt is None:
             fused_sharded = False
     args.shard_effective = opt is not None
+    if ws > 1:
+        _mark("optimizer placement decided: " + ("sharded" if opt is not None else "replicated"))
     if opt is None:
         opt = AdamW(model.parameters(), **kw)
     bucket_fused = hasattr(getattr(opt, "_symm", None), "_reduce_bucket")
@@ -266,6 +315,15 @@ def _arm_watchdog(seconds: float):
 
 def main():
     args = parse_args()
+    ws = int(os.environ.get("WORLD_SIZE", "1"))
+    explicit = (args.optimizer != "auto" or args.zero_variant is not None or args.comm is not None or args.sharded
+                or args.defer_gather != "auto" or args.ddp != "bucketed" or args.no_graph or args.no_overlap)
+    if (args.impl == "ours" and ws > 1 and not args.child and not args.no_guard and not explicit
+            and os.environ.get("B200SYS_BENCH_GUARD", "1") == "1"):
+        try:
+            return guarded_main(args)
+        except Exception as e:  # the guard is a convenience: never let it be the reason there is no number
+            print(f"[bench] guard unavailable ({type(e).__name__}: {e}); running in-process", file=sys.stderr, flush=True)
     watchdog = _arm_watchdog(args.watchdog_s) if args.watchdog_s > 0 else None
     try:
         return _main(args)
@@ -287,10 +345,12 @@ def _main(args):
         print(json.dumps({"impl": args.impl, "unavailable": "no CUDA device"}))
         return 0
     rank, ws, dev = init_dist(args)
+    _mark(f"process group ready ({ws} rank(s))")
     from cs336_a2_systems_b200.utils.clocks import ClockSampler
 
     build = build_ours if args.impl == "ours" else build_reference
     step_device, step_e2e, launches_now, state, extra = build(args, rank, ws, dev)
+    _mark("model, DDP wrapper and optimizer built")
 
     n_pool = 8
     xs_h, ys_h = make_batches(n_pool, args.batch, args.ctx, args.vocab, seed=99 + rank)
@@ -305,7 +365,9 @@ def _main(args):
         loss = step_device(xs_d[i % n_pool], ys_d[i % n_pool])
         if i == 0:
             loss_at[1] = float(loss.item())
+            _mark("first step done")
     torch.cuda.synchronize()
+    _mark(f"{n_warm} warm-up steps done")
     n_launch0 = launches_now() if launches_now is not None else 0
 
     # ---- timed: device-resident inputs
@@ -314,6 +376,7 @@ def _main(args):
     phys = int(vis.split(",")[local]) if vis and vis.split(",")[local].isdigit() else local
     with ClockSampler(phys) as clk:
         ms_dev = timed_loop(lambda i: step_device(xs_d[i % n_pool], ys_d[i % n_pool]), args.steps, ws, dev)
+        _mark("timed loop done")
         # ---- timed: end to end through the public API (pinned host batch in, loss out, every step)
         last = {}
 
@@ -321,6 +384,7 @@ def _main(args):
             last["loss"] = step_e2e(xs_h[i % n_pool], ys_h[i % n_pool])
 
         ms_e2e = timed_loop(e2e, args.steps, ws, dev)
+        _mark("end-to-end loop done")
     clocks = clk.summary()
     n_launched = (launches_now() - n_launch0) if launches_now is not None else None
     comm_dead = None
@@ -341,12 +405,14 @@ def _main(args):
     free_b, total_b = torch.cuda.mem_get_info()
     used_dev = (total_b - free_b) / 2 ** 30  # driver view: also counts NVLink symmetric arenas and the allocator's cache
     peaks = [peak]
+    any_dead = comm_dead is not None
     if ws > 1:
-        t = torch.tensor([peak, used_dev], dtype=torch.float64, device=dev)
+        t = torch.tensor([peak, used_dev, 0.0 if comm_dead is None else 1.0], dtype=torch.float64, device=dev)
         allp = [torch.zeros_like(t) for _ in range(ws)]
         dist.all_gather(allp, t)
         peaks = [float(a[0].item()) for a in allp]
         used_dev = max(float(a[1].item()) for a in allp)
+        any_dead = any(float(a[2].item()) != 0.0 for a in allp)
     if rank == 0:
         from cs336_a2_systems_b200.models import get_model_config
         cfg = get_model_config(args.model)
@@ -387,13 +453,14 @@ def _main(args):
             # ZeRO path): the driver-level figure at the end of the run is the honest memory footprint per GPU
             "device_mem_used_gib_max": round(used_dev, 2),
         }
-        if comm_dead is not None:
-            out["error"] = "NVLink communicator reported a timed-out barrier (rank, cta, peer, phase, slot, flag) = %s" % (comm_dead,)
+        if any_dead:
+            out["error"] = ("NVLink communicator reported a timed-out barrier on some rank; rank 0's record "
+                            "(rank, cta, peer, phase, slot, flag) = %s" % (comm_dead,))
         print(json.dumps(out), flush=True)
     if ws > 1:
         dist.barrier()
         dist.destroy_process_group()
-    return 0
+    return 4 if any_dead else 0  # every rank returns the same code: a watched child is then retried with the next configuration
 
 
 if __name__ == "__main__":

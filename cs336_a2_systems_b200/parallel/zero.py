@@ -66,7 +66,7 @@ def assemble_bucket_state(tensors, offsets, total: int, device=None) -> torch.Te
     return full
 
 
-MAX_EAGER_RANGES = 8  # kZEager in csrc/comm_adamw.cu
+MAX_EAGER_RANGES = 4  # == kZEager in csrc/comm_adamw.cu (the C side rejects more)
 
 
 def eager_ranges(params, offsets, is_eager, align: int = 8):
