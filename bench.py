@@ -203,6 +203,9 @@ def build_ours(args, rank, ws, dev):
             fused_sharded = opt.enable_symmetric(model, defer_fp32_gather=defer, variant=args.zero_variant)
         except Exception as e:  # e.g. the symmetric parameter arenas cannot be mapped on this box
             err = e
+            import traceback
+            print(f"[bench rank {rank}] sharded-optimizer setup failed:", file=sys.stderr, flush=True)
+            traceback.print_exc()  # the other ranks may still be inside a collective of the setup: say why at once
         # every rank must take the same path (the fused kernels meet at cross-rank barriers): agree on the outcome
         ok = torch.tensor([0 if err is not None else 1], device=dev)
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
