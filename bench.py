@@ -460,6 +460,8 @@ def _main(args):
             out["error"] = ("NVLink communicator reported a timed-out barrier on some rank; rank 0's record "
                             "(rank, cta, peer, phase, slot, flag) = %s" % (comm_dead,))
         print(json.dumps(out), flush=True)
+    if not any_dead:
+        _mark("done")
     if ws > 1:
         dist.barrier()
         dist.destroy_process_group()

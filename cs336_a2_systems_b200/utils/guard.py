@@ -28,6 +28,8 @@ import tempfile
 import time
 
 HEARTBEAT_ENV = "B200SYS_HEARTBEAT_FILE"
+#: a child whose last mark is this one has delivered its result: ending it afterwards counts as success
+DONE_MARK = "done"
 _t0 = time.monotonic()
 
 
@@ -120,6 +122,9 @@ def run_attempts(base_cmd: list[str], attempts: list[tuple[str, list[str]]], *, 
                     except OSError:
                         marks = []
                     where = marks[-1].split(" ", 1)[-1] if marks else "start"
+                    if where == DONE_MARK:  # the result is out; only the tear-down of the process group did not return
+                        outcome = "ok"
+                        break
                     outcome = (f"no progress for {now - t_mark:.0f} s after '{where}'" if now - t_mark > stall_s
                                else f"still running after {now - t_start:.0f} s (last mark '{where}')")
                     break

@@ -44,7 +44,7 @@ LAUNCHER = textwrap.dedent("""
     sys.path.insert(0, %(root)r)
     from cs336_a2_systems_b200.utils.guard import run_attempts
     rc, text, hist = run_attempts([sys.executable, %(child)r],
-                                  [("a", ["hang"]), ("b", ["raise"]), ("c", ["ok"])], stall_s=6.0, total_s=60.0)
+                                  [("a", ["hang"]), ("b", ["raise"]), ("c", ["ok"])], stall_s=15.0, total_s=90.0)
     print(json.dumps({"rc": rc, "text": text, "history": hist}), flush=True)
 """)
 
@@ -55,7 +55,7 @@ def _free_port() -> int:
         return s.getsockname()[1]
 
 
-@pytest.mark.timeout(180)
+@pytest.mark.timeout(300)
 def test_two_launchers_fall_back_together(tmp_path):
     child = tmp_path / "child.py"
     child.write_text(CHILD % {"root": ROOT})
@@ -68,7 +68,7 @@ def test_two_launchers_fall_back_together(tmp_path):
                    MASTER_PORT=str(port), TORCHELASTIC_USE_AGENT_STORE="True")
         procs.append(subprocess.Popen([sys.executable, str(launcher)], env=env, stdout=subprocess.PIPE,
                                       stderr=subprocess.PIPE, text=True))
-    outs = [p.communicate(timeout=170) for p in procs]
+    outs = [p.communicate(timeout=280) for p in procs]
     res = []
     for (so, se), p in zip(outs, procs):
         assert p.returncode == 0, se
@@ -93,3 +93,19 @@ def test_all_attempts_fail(tmp_path):
                                   log=lambda m: None)
     assert rc == 1 and text == ""
     assert [h["outcome"] for h in hist] == ["exit code 3", "exit code 5"]
+
+
+def test_child_that_hangs_after_its_result_counts_as_done(tmp_path):
+    from cs336_a2_systems_b200.utils.guard import run_attempts
+
+    script = tmp_path / "late.py"
+    script.write_text(textwrap.dedent("""
+        import sys, time
+        sys.path.insert(0, %r)
+        from cs336_a2_systems_b200.utils.guard import heartbeat, DONE_MARK
+        print('{"value": 1}', flush=True)
+        heartbeat(DONE_MARK, echo=False)
+        time.sleep(3600)
+    """ % ROOT))
+    rc, text, hist = run_attempts([sys.executable, str(script)], [("only", [])], stall_s=10, total_s=60, log=lambda m: None)
+    assert rc == 0 and json.loads(text.strip())["value"] == 1 and hist[0]["outcome"] == "ok"
