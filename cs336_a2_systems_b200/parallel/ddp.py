@@ -197,9 +197,10 @@ class DDPBucketed(_DDPBase):
         order = list(reversed(self._trainable))  # gradients become ready roughly in reverse order
         self.buckets: list[_Bucket] = []
         self._where: dict[int, tuple[int, int]] = {}
-        # in-bucket slot order: forward parameter order; opt-in (B200SYS_FUSE_W13_WGRAD=1, not yet timed on hardware)
-        # the fusion-friendly order that also puts w3 next to w1, so the SwiGLU pair gets ONE wgrad GEMM and — under
-        # the bucket-fused optimizer — an arena-resident bf16 shadow instead of a per-step re-cast
+        # in-bucket slot order: the fusion-friendly order that puts w3 next to w1, so the SwiGLU pair gets ONE wgrad GEMM
+        # and — under the bucket-fused optimizer — an arena-resident bf16 shadow instead of a per-step re-cast (the
+        # default since round 2: every 1/2/8-GPU number of profiles/r2 was measured with it; B200SYS_FUSE_W13_WGRAD=0
+        # restores forward parameter order)
         if os.environ.get("B200SYS_FUSE_W13_WGRAD", "1") == "1":
             slot_pos = {id(p): k for k, p in enumerate(grad_slots.fusion_friendly_order(module))}
         else:

@@ -149,7 +149,7 @@ class Trainer:
             overlap_optimizer = False  # what is left for step() (norm gains, embeddings) is a few microseconds
         self.arena = None
         if grad_arena or (grad_arena is None and self.device.type == "cuda" and not self._is_ddp):
-            # opt-in (not yet timed on hardware): lay w3's slot next to w1's so their wgrads become ONE GEMM
+            # lay w3's slot next to w1's so their wgrads become ONE GEMM (B200SYS_FUSE_W13_WGRAD=0: parameter order)
             fuse_w13 = os.environ.get("B200SYS_FUSE_W13_WGRAD", "1") == "1"
             order = grad_slots.fusion_friendly_order(model) if fuse_w13 else list(model.parameters())
             # weights updated inside their wgrad GEMM never materialise a gradient: no slot (and no memory) for them
