@@ -58,7 +58,8 @@ def parse_args():
                          "of inside the backward-overlapped bucket kernels (bf16 GEMM shadows and fp32-read "
                          "parameters are always distributed at once); 'auto' = off (measured slower at 2 and 8 GPUs)")
     ap.add_argument("--zero-variant", type=int, default=None,
-                    help="ours, sharded: bucket kernel variant (bit 0 NVLS reduce, bit 1 NVLS stores); default by N")
+                    help="ours, sharded: bucket kernel variant (bit 0 NVLS reduce, bit 1 NVLS stores); default 0 (peer "
+                         "loads/stores), 3 = all-NVLS (faster at N > 2 when it runs, see parallel/zero.py)")
     ap.add_argument("--watchdog-s", type=float, default=420.0,
                     help="abort the whole process (exit code 3, one JSON error line) if the run has not finished "
                          "after this many seconds, instead of sitting in a collective until its 10-minute timeout")
@@ -78,7 +79,6 @@ def parse_args():
 #: path; the others exist so that a box on which it stops making progress still yields a measured (and labelled) line.
 GUARD_ATTEMPTS = [
     ("default", []),
-    ("bucket-fused ZeRO-1 kernel with peer loads/stores instead of NVLS", ["--zero-variant", "0"]),
     ("NCCL all-reduce per bucket + replicated AdamW", ["--comm", "c10d", "--optimizer", "replicated"]),
 ]
 

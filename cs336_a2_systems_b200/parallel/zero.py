@@ -125,9 +125,13 @@ class BucketFusedAdamW:
         self._mc = kernels.host_ptr_array(mcs) if have_mc else None
         v = os.environ.get("B200SYS_ZERO_VARIANT", "auto") if variant is None else str(int(variant))
         if v == "auto":
-            # measured (profiles/zero_kernel_n*.json): with 2 ranks plain P2P moves the fewest bytes; from 3 ranks up
-            # the switch reduces the gradient slice and replicates the stores (2.19 vs 2.82 ms/GB at 8 ranks)
-            self.variant = 3 if (have_mc and self.ws > 2) else 0
+            # Peer loads/stores at every world size.  From 3 ranks up the all-NVLS variant (3: the switch reduces the
+            # gradient slice and replicates the stores) is faster when it runs — 2.19 vs 2.82 ms/GB stand-alone, 47.7 vs
+            # 52.1 ms/step end to end at 8 ranks (profiles/r2) — but end-to-end runs with the NVLS variants stopped making
+            # progress at 8 ranks in one call of round 1 and in one call of round 2 (three runs in a row, no barrier
+            # time-out record; cause not identified), while the peer-to-peer variant has never stalled.  Opt in with
+            # variant=3 / B200SYS_ZERO_VARIANT=3.
+            self.variant = 0
         else:
             self.variant = int(v) if have_mc else 0
         #: CTAs per bucket kernel (0 = one per SM): fewer CTAs leave more of each SM's issue slots and memory queues to
