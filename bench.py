@@ -79,7 +79,10 @@ def parse_args():
 #: path; the others exist so that a box on which it stops making progress still yields a measured (and labelled) line.
 GUARD_ATTEMPTS = [
     ("default", []),
-    ("NCCL all-reduce per bucket + replicated AdamW", ["--comm", "c10d", "--optimizer", "replicated"]),
+    # nothing of the first attempt is reused: no symmetric memory, no NVLink kernels, and NCCL without its own NVLS
+    # algorithms (a job that was ended while it used the switch's multicast may leave it unusable for the next one)
+    ("NCCL all-reduce per bucket + replicated AdamW", ["--comm", "c10d", "--optimizer", "replicated"],
+     {"NCCL_NVLS_ENABLE": "0", "B200SYS_MULTIMEM": "0", "B200SYS_COMM": "c10d"}),
 ]
 
 

@@ -52,8 +52,10 @@ def _unique_params(module: nn.Module):
 
 
 @torch.no_grad()
-def broadcast_parameters(module: nn.Module, src: int = 0, group=None, buffers: bool = False) -> None:
-    """Make every rank's parameters equal to ``src``'s with one packed broadcast per (dtype, device)."""
+def broadcast_parameters(module: nn.Module, src: int = 0, group=None, buffers: bool = False,
+                         backend: str | None = None) -> None:
+    """Make every rank's parameters equal to ``src``'s with one packed broadcast per (dtype, device).
+    ``backend``: same choice as the gradient reducer's (None = ``B200SYS_COMM``)."""
     _, ws = world()
     if ws == 1:
         return
@@ -63,7 +65,7 @@ def broadcast_parameters(module: nn.Module, src: int = 0, group=None, buffers: b
     groups: "OrderedDict[tuple, list[torch.Tensor]]" = OrderedDict()
     for t in tensors:
         groups.setdefault((t.dtype, t.device), []).append(t.data)
-    if _comm._choice(None) in ("auto", "symm"):
+    if _comm._choice(backend) in ("auto", "symm"):
         # NVLink path: one pull kernel over a packed symmetric buffer
         from . import symm
         ok, _ = symm.is_legal([t.device for t in tensors], [torch.float32] * len(tensors), group)
@@ -81,7 +83,8 @@ def broadcast_parameters(module: nn.Module, src: int = 0, group=None, buffers: b
 
 
 class _DDPBase(nn.Module):
-    def __init__(self, module: nn.Module, process_group=None, broadcast_buffers: bool = False):
+    def __init__(self, module: nn.Module, process_group=None, broadcast_buffers: bool = False,
+                 backend: str | None = None):
         super().__init__()
         self.module = module
         self.process_group = process_group
@@ -89,7 +92,7 @@ class _DDPBase(nn.Module):
         #: True once an optimizer path that consumes the gradients inside its own reduction has been attached
         #: (ShardedOptimizer.enable_symmetric): ``param.grad`` then holds this rank's local gradient, not the average
         self.grads_are_local = False
-        broadcast_parameters(module, 0, process_group, buffers=broadcast_buffers)
+        broadcast_parameters(module, 0, process_group, buffers=broadcast_buffers, backend=backend)
         self._trainable = [p for p in _unique_params(module) if p.requires_grad]
 
     def forward(self, *args, **kwargs):
@@ -110,7 +113,7 @@ class DDPIndividualParameters(_DDPBase):
     """
 
     def __init__(self, module: nn.Module, process_group=None, backend: str | None = None):
-        super().__init__(module, process_group)
+        super().__init__(module, process_group, backend=backend)
         self._pending: list = []
         self._reducer = None
         if self.world_size > 1:
@@ -192,7 +195,7 @@ class DDPBucketed(_DDPBase):
 
     def __init__(self, module: nn.Module, bucket_size_mb: float | None = None, process_group=None,
                  backend: str | None = None):
-        super().__init__(module, process_group)
+        super().__init__(module, process_group, backend=backend)
         self.bucket_size_mb = bucket_size_mb
         order = list(reversed(self._trainable))  # gradients become ready roughly in reverse order
         self.buckets: list[_Bucket] = []

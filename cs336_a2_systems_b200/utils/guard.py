@@ -74,9 +74,10 @@ def child_env(attempt: int, base_port: int | None = None) -> dict:
     return env
 
 
-def run_attempts(base_cmd: list[str], attempts: list[tuple[str, list[str]]], *, stall_s: float = 75.0,
+def run_attempts(base_cmd: list[str], attempts: list[tuple], *, stall_s: float = 75.0,
                  total_s: float = 300.0, poll_s: float = 0.25, log=None) -> tuple[int, str, list[dict]]:
-    """Run ``base_cmd + extra`` for each ``(label, extra)`` in ``attempts`` until one exits 0.
+    """Run ``base_cmd + extra`` for each ``(label, extra)`` or ``(label, extra, extra_env)`` in ``attempts`` until one
+    exits 0.
 
     Returns ``(exit code, stdout of the successful child or "", history)``; ``history`` has one entry per attempt:
     ``{"config": label, "outcome": "ok" | "exit code N" | "no progress for S s after '<last mark>'" | ...}``.
@@ -93,10 +94,13 @@ def run_attempts(base_cmd: list[str], attempts: list[tuple[str, list[str]]], *, 
 
     old = {s: signal.signal(s, on_term) for s in (signal.SIGTERM, signal.SIGINT)}
     try:
-        for k, (label, extra) in enumerate(attempts):
+        for k, att in enumerate(attempts):
+            label, extra = att[0], list(att[1])
             hb = tempfile.NamedTemporaryFile("w", prefix="b200_hb_", suffix=".log", delete=False)
             hb.close()
             env = child_env(k)
+            if len(att) > 2 and att[2]:
+                env.update(att[2])
             env[HEARTBEAT_ENV] = hb.name
             out = tempfile.TemporaryFile("w+")
             t_start = time.monotonic()
