@@ -338,6 +338,20 @@ def main():
             return guarded_main(args)
         except Exception as e:  # the guard is a convenience: never let it be the reason there is no number
             print(f"[bench] guard unavailable ({type(e).__name__}: {e}); running in-process", file=sys.stderr, flush=True)
+    if args.child:
+        # a watched child must not outlive its launcher (it runs in its own session, so torchrun's signals only reach
+        # the launcher): end it when it has been re-parented
+        import threading
+        import time as _time
+        ppid0 = os.getppid()
+
+        def _watch_parent():
+            while True:
+                _time.sleep(2.0)
+                if os.getppid() != ppid0:
+                    os._exit(1)
+
+        threading.Thread(target=_watch_parent, daemon=True).start()
     watchdog = _arm_watchdog(args.watchdog_s) if args.watchdog_s > 0 else None
     try:
         return _main(args)
